@@ -1,0 +1,301 @@
+/*
+ * spt.h — C ABI of the B200-native wavefront path-tracing core.
+ *
+ * This is the drop-in boundary for the hot path of PepcyCh/simple-path-tracer.  The reference
+ * is a single Rust binary without FFI; the two trait seams this library replaces are
+ *
+ *   B1  RendererT::render(&self, scene: &Scene, config: &OutputConfig)
+ *         src/renderer/mod.rs:16-19   (variant picked by create_renderer, mod.rs:26-38)
+ *   B2  PrimitiveT::intersect(&self, ray, inter) -> bool        src/primitive/mod.rs:27
+ *       PrimitiveT::intersect_test(&self, ray, t_max) -> bool   src/primitive/mod.rs:25
+ *         both invoked on scene.aggregate(), src/core/scene.rs:43-45
+ *
+ * A Rust host would flatten its `Scene` (src/core/scene.rs:7-12) into an SptSceneDesc once,
+ * then call spt_render from a new `Renderer::Wavefront` variant.
+ *
+ * Conventions: plain C, no exceptions cross the boundary.  Every entry point returns an
+ * int32_t status (0 = SPT_OK); the message of the last failure on the calling thread is
+ * available from spt_last_error().  All pointers inside descriptors are caller-owned HOST
+ * memory that is copied during the call (the library never keeps host pointers), except
+ * where a parameter is explicitly named d_* (device pointer).  Handles are opaque and are
+ * released by *_destroy.  Calls on one handle are not thread-safe; handles are independent.
+ *
+ * There is NO CPU fallback: without a CUDA device every compute entry point fails with
+ * SPT_ERR_CUDA.
+ */
+#ifndef SPT_H_
+#define SPT_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPT_OK 0
+#define SPT_ERR_INVALID 1 /* bad argument / inconsistent descriptor */
+#define SPT_ERR_CUDA 2    /* CUDA runtime error (incl. "no device") */
+#define SPT_ERR_UNSUPPORTED 3
+
+/* ---- enumerations (values are part of the ABI) ------------------------------------------ */
+
+/* primitive kinds — src/primitive/mod.rs:40-53 (only the in-scope leaves) */
+enum { SPT_PRIM_SPHERE = 0, SPT_PRIM_TRIMESH = 1 };
+
+/* material tags — src/material/mod.rs:33-45 (P-NDF variants out of scope) */
+enum {
+  SPT_MAT_LAMBERT = 0,      /* tex[0]=albedo                                  lambert.rs:26-31  */
+  SPT_MAT_PSEUDO = 1,       /* no parameters                                   pseudo.rs:20-24   */
+  SPT_MAT_CONDUCTOR = 2,    /* tex[0]=ior tex[1]=ior_k tex[2]=rough_x tex[3]=rough_y  conductor.rs:50-73 */
+  SPT_MAT_DIELECTRIC = 3,   /* ior; tex[0]=reflectance tex[1]=transmittance (both ignored, Q11) tex[2..3]=rough */
+  SPT_MAT_PLASTIC = 4,      /* ior; tex[0]=albedo tex[2..3]=rough (NOT squared, Q12)  plastic.rs:60-82 */
+  SPT_MAT_PBR_METALLIC = 5, /* tex[0]=base_color tex[1]=metallic tex[2..3]=rough  pbr_metallic.rs:67-98 */
+  SPT_MAT_PBR_SPECULAR = 6, /* tex[0]=diffuse tex[1]=specular tex[2..3]=rough     pbr_specular.rs:60-88 */
+  SPT_MAT_SUBSURFACE = 7    /* ior; tex[0]=albedo tex[1]=ld tex[2..3]=rough        subsurface.rs:65-94  */
+};
+
+/* texture tags — src/texture/mod.rs:198-208 */
+enum {
+  SPT_TEX_SCALAR = 0, /* value[3]                                     scalar.rs:21-51 */
+  SPT_TEX_IMAGE = 1,  /* RGBA8 image, mip chain built by the library  image_tex.rs:63-153 */
+  SPT_TEX_ADD = 2,    /* child[0] + child[1]                          binary_op.rs:68-73 */
+  SPT_TEX_SUB = 3,
+  SPT_TEX_MUL = 4,
+  SPT_TEX_DIV = 5,
+  SPT_TEX_SRGB = 6,          /* srgb->linear of child[0]              srgb_tex.rs:17-69 */
+  SPT_TEX_INPUT_MODIFIER = 7 /* tiling/offset/mode/wrap over child[0] input_modifier.rs:34-97 */
+};
+/* TextureInputMode — src/texture/mod.rs:21-29 ; -1 = "None" in TexInputModifier */
+enum { SPT_TEXMODE_SPECIFIED = 0, SPT_TEXMODE_TEXCOORDS = 1, SPT_TEXMODE_POSITION = 2,
+       SPT_TEXMODE_NORMAL = 3, SPT_TEXMODE_TANGENT = 4, SPT_TEXMODE_BITANGENT = 5 };
+/* TextureInputWrapMode — src/texture/mod.rs:37-43 ; -1 = "None" */
+enum { SPT_TEXWRAP_REPEAT = 0, SPT_TEXWRAP_MIRROR_REPEAT = 1, SPT_TEXWRAP_CLAMP = 2,
+       SPT_TEXWRAP_MIRROR_CLAMP = 3 };
+/* TextureChannel — src/texture/mod.rs:165-171 */
+enum { SPT_CHAN_R = 0, SPT_CHAN_G = 1, SPT_CHAN_B = 2, SPT_CHAN_A = 3 };
+
+/* light tags — src/light/mod.rs:28-35 */
+enum { SPT_LIGHT_DIRECTIONAL = 0, SPT_LIGHT_POINT = 1, SPT_LIGHT_SPOT = 2, SPT_LIGHT_SHAPE = 3,
+       SPT_LIGHT_ENV = 4 };
+/* light sampler — src/light_sampler/mod.rs:37-41 */
+enum { SPT_LS_UNIFORM = 0, SPT_LS_POWER_IS = 1 };
+/* pixel sampler — src/pixel_sampler/mod.rs */
+enum { SPT_SAMPLER_RANDOM = 0, SPT_SAMPLER_JITTERED = 1, SPT_SAMPLER_RECURRENCE = 2 };
+/* aggregate — src/core/scene_resources.rs:85-103 (informational: results are aggregate-independent) */
+enum { SPT_AGG_GROUP = 0, SPT_AGG_BVH = 1 };
+
+/* ---- scene description: flat, index-linked mirror of core/scene.rs:7-12 ----------------- */
+
+typedef struct SptMeshDesc { /* TriMesh — src/primitive/triangle.rs:10-27 */
+  int32_t n_verts, n_tris;
+  const float* position;  /* 3*n_verts */
+  const float* normal;    /* 3*n_verts */
+  const float* texcoord;  /* 2*n_verts */
+  const float* tangent;   /* 3*n_verts */
+  const float* bitangent; /* 3*n_verts */
+  const uint32_t* index;  /* 3*n_tris  */
+} SptMeshDesc;
+
+typedef struct SptSphereDesc { /* src/primitive/sphere.rs:8-12 */
+  float center[3];
+  float radius;
+} SptSphereDesc;
+
+typedef struct SptInstanceDesc { /* src/primitive/instance.rs:10-16 */
+  int32_t prim_kind;  /* SPT_PRIM_* */
+  int32_t prim_index; /* into spheres[] or meshes[] */
+  int32_t surface;    /* into surfaces[] */
+  float xform[12];    /* glam::Affine3A, column-major: x_axis, y_axis, z_axis, translation */
+} SptInstanceDesc;
+
+typedef struct SptSurfaceDesc { /* src/core/surface.rs:14-22 */
+  int32_t material;
+  int32_t normal_map; /* texture or -1 */
+  float emissive[3];
+  int32_t emissive_map; /* texture or -1 */
+  int32_t double_sided;
+  int32_t inside_medium; /* medium or -1 */
+} SptSurfaceDesc;
+
+typedef struct SptMaterialDesc { /* src/material/ (one file per tag) */
+  int32_t tag;
+  int32_t tex[4];
+  float ior;          /* int_ior / ext_ior */
+  int32_t rough_chan; /* SPT_CHAN_*  (pbr_*: roughness_chan) */
+  int32_t metal_chan; /* SPT_CHAN_*  (pbr_metallic: metallic_chan) */
+} SptMaterialDesc;
+
+typedef struct SptTextureDesc { /* src/texture/ */
+  int32_t tag;
+  int32_t child[2];
+  float value[3];
+  float tiling[3], offset[3];
+  int32_t mode, wrap;  /* SPT_TEXMODE_* / SPT_TEXWRAP_* or -1 */
+  int32_t width, height;
+  const uint8_t* rgba; /* width*height*4, row-major, only SPT_TEX_IMAGE */
+} SptTextureDesc;
+
+typedef struct SptMediumDesc { /* src/medium/homogeneous.rs:5-9 (sigma_s as LOADED, i.e. after Q13) */
+  float sigma_a[3], sigma_s[3];
+  float asymmetric;
+} SptMediumDesc;
+
+typedef struct SptLightDesc { /* src/light/; listed in the order of the light sampler's Vec */
+  int32_t tag;
+  float position[3];
+  float direction[3]; /* as loaded (DirLight::new normalises it, SpotLight does not) */
+  float strength[3];
+  float inner_angle, outer_angle; /* radians */
+  int32_t instance;               /* SPT_LIGHT_SHAPE: index into instances[] */
+} SptLightDesc;
+
+typedef struct SptEnvDesc { /* src/light/environment.rs:9-16 */
+  int32_t width, height;
+  const float* rgb; /* height rows of width texels, 3 floats each */
+  float scale[3];
+} SptEnvDesc;
+
+typedef struct SptCameraDesc { /* src/camera/perspective.rs:5-12 */
+  float eye[3], forward[3], up[3];
+  float fov; /* radians */
+} SptCameraDesc;
+
+typedef struct SptSceneDesc {
+  int32_t n_meshes;    const SptMeshDesc* meshes;
+  int32_t n_spheres;   const SptSphereDesc* spheres;
+  int32_t n_instances; const SptInstanceDesc* instances;
+  int32_t n_surfaces;  const SptSurfaceDesc* surfaces;
+  int32_t n_materials; const SptMaterialDesc* materials;
+  int32_t n_textures;  const SptTextureDesc* textures;
+  int32_t n_mediums;   const SptMediumDesc* mediums;
+  int32_t n_lights;    const SptLightDesc* lights;
+  int32_t n_cameras;   const SptCameraDesc* cameras;
+  const SptEnvDesc* env;    /* NULL = none */
+  int32_t env_light_index;  /* Q8 (scene_resources.rs:165); -1 = none */
+  int32_t light_sampler;    /* SPT_LS_* */
+  int32_t aggregate;        /* SPT_AGG_* */
+} SptSceneDesc;
+
+/* ---- ray queries (seam B2) ---------------------------------------------------------------- */
+
+typedef struct SptRay { /* core/ray.rs:1-27; direction is NOT required to be unit length */
+  float origin[3];
+  float t_min;
+  float direction[3];
+  float t_max; /* Intersection::t on entry (f32::MAX = unbounded), core/intersection.rs:21-26 */
+} SptRay;
+
+typedef struct SptHit { /* the identity part of core/intersection.rs:6-18 */
+  float t;         /* hit distance; t_max of the ray on a miss */
+  float u, v;      /* triangle: barycentric weights of vertex 1 and 2 (reference's v,w; triangle.rs:124-147);
+                      sphere: texcoords (sphere.rs:138-145) */
+  int32_t prim_id; /* triangle index inside its mesh (file order), 0 for a sphere, -1 on a miss */
+  int32_t inst_id; /* index into SptSceneDesc::instances, -1 on a miss */
+} SptHit;
+
+/* ---- BxDF test hook (BxdfT::{sample,pdf,bxdf,is_delta}, src/bxdf/mod.rs:80-90) -------------- */
+
+typedef struct SptBxdfQuery {
+  int32_t material;  /* index into materials[] */
+  float texcoord[2]; /* inter.texcoords fed to MaterialT::bxdf_context */
+  float wo[3];       /* local frame, z = shading normal */
+  float wi[3];       /* direction for pdf()/bxdf() */
+  float rand[8];     /* the uniform_1d() draws, consumed in call order by sample() */
+} SptBxdfQuery;
+
+typedef struct SptBxdfResult {
+  float sample_wi[3];
+  float sample_f[3];
+  float sample_pdf;
+  int32_t sample_lobe; /* 0 diffuse 1 glossy 2 specular  (BxdfLobeType) */
+  int32_t sample_dir;  /* 0 reflect 1 transmit           (BxdfDirType)  */
+  int32_t n_rand_used;
+  float eval_f[3]; /* bxdf(wo, wi) */
+  float eval_pdf;  /* pdf(wo, wi)  */
+  int32_t is_delta;
+  int32_t bxdf_tag; /* which Bxdf variant bxdf_context() built (bxdf/mod.rs:92-102 order) */
+} SptBxdfResult;
+
+/* ---- render (seam B1) ------------------------------------------------------------------------- */
+
+#define SPT_RENDER_COUNT_TRAVERSAL 1u /* fill nodes_visited/tris_tested/insts_visited (slower build) */
+#define SPT_RENDER_NO_SORT 2u         /* disable material binning of the shade stage (for A/B timing) */
+
+typedef struct SptRenderDesc { /* OutputConfig (renderer/mod.rs:9-14) + PathTracer fields (pt.rs:24-28) */
+  int32_t camera_index;
+  int32_t width, height;
+  int32_t max_depth;       /* scenes/pt.json:3 */
+  int32_t sampler_kind;    /* SPT_SAMPLER_* */
+  int32_t spp;             /* random / recurrence */
+  int32_t div_x, div_y;    /* jittered (spp = div_x*div_y) */
+  float filter_radius;     /* box filter, filter/boxf.rs; only r <= 0.5 (own-pixel mean, Q14) is supported */
+  uint64_t seed;           /* RNG key; the stream of a path depends only on (seed, pixel, sample) */
+  int32_t tile_w, tile_h;  /* screen tile size for rank interleaving (0 = 32) */
+  int32_t rank, world_size;/* this process renders the tiles it owns; others stay 0 */
+  int32_t pool_size;       /* resident path slots (0 = default 2^20) */
+  uint32_t flags;
+} SptRenderDesc;
+
+typedef struct SptStats {
+  uint64_t paths;          /* camera samples traced by this rank */
+  uint64_t ext_rays;       /* closest-hit rays (pt.rs:50) */
+  uint64_t shadow_rays;    /* any-hit rays (pt.rs:81,169) */
+  uint64_t probe_rays;     /* BSSRDF probes (substrate.rs:290) */
+  uint64_t nodes_visited, tris_tested, insts_visited; /* only with SPT_RENDER_COUNT_TRAVERSAL */
+  uint64_t nonfinite;      /* contributions dropped because they were NaN/Inf */
+  uint64_t iterations;     /* wavefront iterations */
+  uint64_t kernel_launches;
+  double seconds_total;    /* device time of the whole render (CUDA events) */
+  double seconds_stage[6]; /* generate, extend, shade, connect, resolve, other */
+} SptStats;
+
+typedef struct SptSceneInfo {
+  int64_t tlas_nodes, blas_nodes, triangles, instances;
+  int64_t bytes_nodes, bytes_tris, bytes_total;
+} SptSceneInfo;
+
+typedef struct SptContext SptContext;
+typedef struct SptScene SptScene;
+
+const char* spt_last_error(void);
+int32_t spt_version(void);
+
+/* One context = one CUDA device (one process per GPU; ranks are joined by the host with NCCL). */
+int32_t spt_context_create(int32_t device_id, SptContext** out);
+int32_t spt_context_destroy(SptContext* ctx);
+
+/* Flatten + host wide-BVH build + upload.  Replaces BvhAccel::new (primitive/bvh.rs:23-141),
+ * TriMesh::new (triangle.rs:42-55), Instance::new (instance.rs:19-29), EnvLight::new
+ * (environment.rs:18-50), PowerIsLightSampler::new (power_is.rs:19-42). */
+int32_t spt_scene_create(SptContext* ctx, const SptSceneDesc* desc, SptScene** out);
+/* Re-send the already flattened scene arrays host->device (pinned staging; no rebuild). */
+int32_t spt_scene_upload(SptScene* scene, int64_t* bytes_copied);
+int32_t spt_scene_info(const SptScene* scene, SptSceneInfo* out);
+int32_t spt_scene_destroy(SptScene* scene);
+
+/* ≙ PrimitiveT::intersect on scene.aggregate() for n rays (host buffers). */
+int32_t spt_trace_batch(SptScene* scene, const SptRay* rays, int64_t n, SptHit* out_hits);
+/* ≙ PrimitiveT::intersect_test (ray.t_max is the t_max argument); out[i] = 1 if occluded. */
+int32_t spt_occluded_batch(SptScene* scene, const SptRay* rays, int64_t n, uint8_t* out);
+/* Same, buffers already resident in device memory; stats may be NULL; runs on `stream`
+ * (a cudaStream_t passed as void*, NULL = default stream) without synchronising. */
+int32_t spt_trace_batch_device(SptScene* scene, const SptRay* d_rays, int64_t n, SptHit* d_hits,
+                               uint32_t flags, SptStats* stats, void* stream);
+int32_t spt_occluded_batch_device(SptScene* scene, const SptRay* d_rays, int64_t n, uint8_t* d_out,
+                                  uint32_t flags, SptStats* stats, void* stream);
+
+/* Test hook ≙ BxdfT::{sample,pdf,bxdf,is_delta} with caller-supplied random numbers. */
+int32_t spt_bxdf_batch(SptScene* scene, const SptBxdfQuery* queries, int64_t n, SptBxdfResult* out);
+
+/* ≙ RendererT::render.  out_rgb_mean: width*height*3 f32, row 0 = top (film.rs:64-66);
+ * out_rgb8 (optional): the 8-bit encode of film.rs:94-99.  Both are HOST buffers. */
+int32_t spt_render(SptScene* scene, const SptRenderDesc* desc, float* out_rgb_mean, uint8_t* out_rgb8,
+                   SptStats* stats);
+/* Same, result left in device memory (width*height*3 f32; pixels of other ranks are 0) so the
+ * host can reduce it over NCCL without a round trip. */
+int32_t spt_render_device(SptScene* scene, const SptRenderDesc* desc, float* d_rgb_mean, SptStats* stats);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPT_H_ */

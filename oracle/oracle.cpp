@@ -1,0 +1,517 @@
+// oracle/oracle.cpp — TEST INFRASTRUCTURE ONLY (the parity checker and the timed CPU baseline).
+//
+// CPU restatement of the hot path of PepcyCh/simple-path-tracer, following the Rust sources line by
+// line (each function cites the file:line it follows).  PARITY UNPINNED: the reference has no tests,
+// golden vectors or fixtures and cannot be compiled in this image (no cargo/rustc,
+// no Cargo.lock, un-vendored git dependency), so this restatement is pinned only by review against
+// the cited lines and by the closed-form known-answer tests in tests/test_oracle_kat.py.
+//
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load
+// this library.  It shares no code with simple-path-tracer_b200/csrc; the only common file is the
+// public interface header include/spt.h (scene description structs).
+//
+// Deliberate deviations from the reference (none changes results for the benchmarked settings):
+//  * Film (core/film.rs) is a running per-pixel f32 sum instead of a Vec of every sample; identical
+//    for the box filter with radius <= 0.5 (Q14), which is all spt.h supports.
+//  * SmallRng::from_entropy (rng.rs:10) -> xoshiro256++ seeded from (seed, thread); HashMap iteration
+//    order (Q9) -> the order of the arrays in SptSceneDesc.
+//  * JitteredSampler (Q16) terminates after div_x*div_y samples (the evident intent).
+//  * A path that is inside a medium and whose ray leaves the scene would panic in the reference
+//    (pt.rs:77 unwrap on None); here it is terminated.
+#include <thread>
+#include <atomic>
+#include <mutex>
+#include <cstring>
+#include <string>
+#include <chrono>
+#include <functional>
+#include "../include/spt.h"
+#include "lights.h"
+
+using namespace orc;
+
+namespace {
+
+struct Camera { // camera/perspective.rs:5-12
+  Vec3 eye, forward, up, right; float half_cot_half_fov = 1;
+  void init(Vec3 e, Vec3 f, Vec3 u, float fov) { // :15-27
+    eye = e; forward = normalize(f); right = normalize(cross(forward, u)); up = cross(right, forward);
+    half_cot_half_fov = 0.5f / std::tan(fov * 0.5f);
+  }
+  Ray generate_ray(float px, float py) const { // :41-47
+    return Ray(eye, normalize(forward * half_cot_half_fov + right * px + up * py));
+  }
+  Ray generate_ray_with_aux_ray(float px, float py, float ox, float oy) const { // camera/mod.rs:15-21
+    Ray r = generate_ray(px, py);
+    Ray rx = generate_ray(px + ox, py), ry = generate_ray(px, py + oy);
+    r.has_aux = true;
+    r.aux = {rx.origin, rx.direction, ry.origin, ry.direction};
+    return r;
+  }
+};
+
+inline Vec3 v3(const float* p) { return {p[0], p[1], p[2]}; }
+inline Color c3(const float* p) { return {p[0], p[1], p[2]}; }
+
+} // namespace
+
+struct OrcScene {
+  TextureTable textures;
+  std::vector<Material> materials;
+  std::vector<Medium> mediums;
+  std::vector<Surface> surfaces;
+  std::vector<Sphere> spheres;
+  std::vector<std::unique_ptr<TriMesh>> meshes;
+  std::vector<Instance> instances;
+  Aggregate aggregate;
+  EnvLight env; bool has_env = false;
+  LightSampler light_sampler;
+  std::vector<Camera> cameras;
+};
+
+static thread_local std::string g_err;
+extern "C" const char* orc_last_error() { return g_err.c_str(); }
+
+extern "C" int32_t orc_scene_create(const SptSceneDesc* d, OrcScene** out) {
+  if (!d || !out) { g_err = "null argument"; return SPT_ERR_INVALID; }
+  auto S = std::make_unique<OrcScene>();
+  S->textures.tex.resize(d->n_textures);
+  for (int i = 0; i < d->n_textures; i++) {
+    const SptTextureDesc& t = d->textures[i];
+    Texture& o = S->textures.tex[i];
+    o.tag = t.tag; o.child[0] = t.child[0]; o.child[1] = t.child[1];
+    o.value = c3(t.value); o.tiling = v3(t.tiling); o.offset = v3(t.offset); o.mode = t.mode; o.wrap = t.wrap;
+    if (t.tag == SPT_TEX_IMAGE) {
+      if (!t.rgba || t.width <= 0 || t.height <= 0) { g_err = "image texture without pixels"; return SPT_ERR_INVALID; }
+      Image8 im; im.w = t.width; im.h = t.height; im.px.assign(t.rgba, t.rgba + (size_t)4 * t.width * t.height);
+      o.images = generate_mipmap(std::move(im));
+    }
+  }
+  S->materials.resize(d->n_materials);
+  for (int i = 0; i < d->n_materials; i++) {
+    const SptMaterialDesc& m = d->materials[i];
+    Material& o = S->materials[i];
+    o.tag = m.tag; for (int k = 0; k < 4; k++) o.tex[k] = m.tex[k];
+    o.ior = m.ior; o.rough_chan = m.rough_chan; o.metal_chan = m.metal_chan;
+  }
+  S->mediums.resize(d->n_mediums);
+  for (int i = 0; i < d->n_mediums; i++) S->mediums[i].init(c3(d->mediums[i].sigma_a), c3(d->mediums[i].sigma_s), d->mediums[i].asymmetric);
+  S->surfaces.resize(d->n_surfaces);
+  for (int i = 0; i < d->n_surfaces; i++) {
+    const SptSurfaceDesc& s = d->surfaces[i];
+    Surface& o = S->surfaces[i];
+    if (s.material < 0 || s.material >= d->n_materials) { g_err = "surface: bad material index"; return SPT_ERR_INVALID; }
+    o.material = &S->materials[s.material]; o.normal_map = s.normal_map; o.emissive_v = c3(s.emissive);
+    o.emissive_map = s.emissive_map; o.double_sided = s.double_sided != 0;
+    o.inside_medium_v = s.inside_medium >= 0 ? &S->mediums[s.inside_medium] : nullptr;
+    o.T = &S->textures;
+  }
+  S->spheres.resize(d->n_spheres);
+  for (int i = 0; i < d->n_spheres; i++) S->spheres[i].init(v3(d->spheres[i].center), d->spheres[i].radius);
+  for (int i = 0; i < d->n_meshes; i++) {
+    const SptMeshDesc& m = d->meshes[i];
+    auto mesh = std::make_unique<TriMesh>();
+    mesh->mesh_id = i;
+    mesh->vertices.resize(m.n_verts);
+    for (int v = 0; v < m.n_verts; v++) {
+      MeshVertex& mv = mesh->vertices[v];
+      mv.position = v3(m.position + 3 * v); mv.normal = v3(m.normal + 3 * v);
+      mv.texcoords = {m.texcoord[2 * v], m.texcoord[2 * v + 1]};
+      mv.tangent = v3(m.tangent + 3 * v); mv.bitangent = v3(m.bitangent + 3 * v);
+    }
+    std::vector<uint32_t> idx(m.index, m.index + (size_t)3 * m.n_tris);
+    mesh->build(idx);
+    S->meshes.push_back(std::move(mesh));
+  }
+  S->instances.resize(d->n_instances);
+  for (int i = 0; i < d->n_instances; i++) {
+    const SptInstanceDesc& in = d->instances[i];
+    Shape sh;
+    if (in.prim_kind == SPT_PRIM_SPHERE) sh.sphere = &S->spheres.at(in.prim_index);
+    else sh.mesh = S->meshes.at(in.prim_index).get();
+    Affine3 a;
+    a.m.x = v3(in.xform); a.m.y = v3(in.xform + 3); a.m.z = v3(in.xform + 6); a.t = v3(in.xform + 9);
+    S->instances[i].init(sh, a, &S->surfaces.at(in.surface), i);
+  }
+  std::vector<const Instance*> ptrs;
+  for (auto& in : S->instances) ptrs.push_back(&in);
+  S->aggregate.use_bvh = d->aggregate != SPT_AGG_GROUP; // scene_resources.rs:85-103
+  if (S->aggregate.use_bvh) S->aggregate.bvh.build(ptrs, 4, 16); else S->aggregate.group = ptrs;
+  if (d->env) {
+    std::vector<Color> tex((size_t)d->env->width * d->env->height);
+    for (size_t i = 0; i < tex.size(); i++) tex[i] = c3(d->env->rgb + 3 * i);
+    S->env.init(std::move(tex), d->env->width, d->env->height, c3(d->env->scale));
+    S->has_env = true;
+  }
+  LightSampler& ls = S->light_sampler;
+  ls.kind = d->light_sampler; ls.env_light_index = d->env_light_index;
+  ls.instance_light.assign(d->n_instances, -1);
+  ls.lights.resize(d->n_lights);
+  for (int i = 0; i < d->n_lights; i++) {
+    const SptLightDesc& l = d->lights[i];
+    Light& o = ls.lights[i];
+    o.tag = l.tag; o.position = v3(l.position); o.strength = c3(l.strength);
+    o.direction = l.tag == SPT_LIGHT_DIRECTIONAL ? normalize(v3(l.direction)) : v3(l.direction); // directional.rs:13
+    o.cos_inner = std::cos(l.inner_angle); o.cos_outer = std::cos(l.outer_angle);             // spot.rs:22-23
+    if (l.tag == SPT_LIGHT_SHAPE) { o.shape = &S->instances.at(l.instance); ls.instance_light[l.instance] = i; }
+    if (l.tag == SPT_LIGHT_ENV) { if (!S->has_env) { g_err = "env light without env"; return SPT_ERR_INVALID; } o.env = &S->env; }
+  }
+  if (d->n_lights > 0) ls.init(S->textures);
+  S->cameras.resize(d->n_cameras);
+  for (int i = 0; i < d->n_cameras; i++) S->cameras[i].init(v3(d->cameras[i].eye), v3(d->cameras[i].forward), v3(d->cameras[i].up), d->cameras[i].fov);
+  *out = S.release();
+  return SPT_OK;
+}
+
+extern "C" void orc_scene_destroy(OrcScene* s) { delete s; }
+
+// ---- renderer/pt.rs -------------------------------------------------------------------------------
+namespace {
+
+struct PathStats { uint64_t ext = 0, shadow = 0, probe = 0, nonfinite = 0; };
+
+inline float power_heuristic(float p0, float p1) { // pt.rs:298-302 (n0 = n1 = 1)
+  float a = 1.0f * p0, b = 1.0f * p1;
+  return a * a / (a * a + b * b);
+}
+
+// PathTracer::shadow_ray_from_medium, pt.rs:212-233.  NB: the leaf primitive is intersected with the
+// WORLD-space ray although its data is in object space — reproduced as written.
+inline Ray shadow_ray_from_medium(Vec3 p, Vec3 light_dir, float light_dist, const PrimRef& prim, float& transported) {
+  Ray sr(p, light_dir);
+  Intersection tmp = Intersection::with_t_max(light_dist - 0.001f);
+  if (primref_intersect(prim, sr, tmp)) { transported = tmp.t; sr.t_min += tmp.t; }
+  else { transported = light_dist; sr.t_min += light_dist - 0.001f; }
+  return sr;
+}
+
+Color trace_ray(const OrcScene& sc, Ray ray, Rng& rng, int max_depth, PathStats& st) { // pt.rs:39-210
+  Color final_color = BLACK, throughput = WHITE;
+  int curr_depth = 0;
+  const Medium* curr_medium = nullptr;
+  PrimRef curr_primitive;
+  LightSamplerInputs lsi{};
+  float last_sample_pdf = 0.0f;
+  const LightSampler& ls = sc.light_sampler;
+  const bool have_lights = !ls.lights.empty();
+
+  while (curr_depth < max_depth) {
+    Intersection inter;
+    st.ext++;
+    bool does_hit = sc.aggregate.intersect(ray, inter);
+    if (does_hit) inter.calc_differential(ray);
+    curr_primitive = inter.primitive;
+
+    if (curr_medium) { // pt.rs:56-96
+      Vec3 wo = -ray.direction;
+      bool still_in; Color attenuation;
+      Vec3 pi = curr_medium->sample_pi(ray.origin, wo, inter.t, rng, still_in, attenuation);
+      throughput *= attenuation;
+      if (!still_in) { curr_medium = nullptr; continue; }
+      if (curr_primitive.kind == PrimRef::kNone) break; // reference would panic (unwrap on None)
+      Color li = BLACK;
+      lsi = {pi, Vec3(0, 0, 0)};
+      if (have_lights) {
+        float pdf, dist; Color L; bool delta;
+        Vec3 light_dir = ls.sample_light(lsi, rng, pdf, L, dist, delta);
+        float phase = curr_medium->phase(wo, light_dir);
+        float transported;
+        Ray shadow = shadow_ray_from_medium(pi, light_dir, dist, curr_primitive, transported);
+        Color atten = curr_medium->transport_attenuation(transported);
+        if (pdf != 0.0f && std::isfinite(pdf)) {
+          st.shadow++;
+          if (!sc.aggregate.intersect_test(shadow, dist - 0.001f)) {
+            if (delta) li = atten * phase * L / pdf;
+            else { float w = power_heuristic(pdf, phase); li = atten * phase * L * w / pdf; }
+          }
+        }
+      }
+      final_color += throughput * li;
+      float pdf;
+      Vec3 wi = curr_medium->sample_wi(wo, rng, pdf);
+      last_sample_pdf = pdf;
+      ray = Ray(pi, wi);
+    } else if (!does_hit) { // pt.rs:97-111
+      if (sc.has_env) {
+        Color env; float dist, env_pdf;
+        sc.env.strength_dist_pdf(ray.direction, env, dist, env_pdf);
+        float weight = curr_depth == 0 ? 1.0f : power_heuristic(last_sample_pdf, ls.pdf_env_light() * env_pdf);
+        final_color += throughput * env * weight;
+      }
+      break;
+    } else { // pt.rs:112-193
+      Vec3 po = ray.point_at(inter.t);
+      const Surface* surf = inter.surface;
+      Bxdf bxdf = surf->material->bxdf_context(sc.textures, inter); // surface.rs:97-103
+      Coordinate coord_po = surf->coord(ray, inter);
+      Color li_emissive = surf->emissive(inter);
+      if (li_emissive.luminance() > 0.0f) {
+        float weight = curr_depth == 0 ? 1.0f : power_heuristic(last_sample_pdf, ls.pdf_shape_light(lsi, inter.instance, inter));
+        final_color += throughput * li_emissive * weight;
+      }
+      Vec3 wo = coord_po.to_local(-ray.direction);
+      BxdfInputs bin{po, coord_po, wo, &sc.aggregate, &st.probe};
+      BxdfSample samp = bxdf.sample(bin, rng);
+      if (samp.has_ss) {
+        po = samp.ss.pi; coord_po = samp.ss.coord_pi;
+        throughput *= samp.ss.sp / samp.ss.pdf_pi;
+      }
+      Color li = BLACK;
+      lsi = {po, inter.normal};
+      if (!bxdf.is_delta() && have_lights) {
+        float pdf, dist; Color L; bool delta;
+        Vec3 light_dir = ls.sample_light(lsi, rng, pdf, L, dist, delta);
+        Vec3 wi = coord_po.to_local(light_dir);
+        Color f = bxdf.bxdf(wo, wi);
+        float mat_pdf = bxdf.pdf(wo, wi);
+        Ray shadow(po, light_dir);
+        shadow.t_min = T_MIN_EPS / fmax_(std::fabs(wi.z), 0.00001f);
+        if (pdf != 0.0f && std::isfinite(pdf)) {
+          st.shadow++;
+          if (!sc.aggregate.intersect_test(shadow, dist - 0.001f)) {
+            if (delta) li = L * f * std::fabs(wi.z) / fmax_(pdf, 0.00001f);
+            else { float w = power_heuristic(pdf, mat_pdf); li = L * f * std::fabs(wi.z) * w / fmax_(pdf, 0.00001f); }
+          }
+        }
+        final_color += throughput * li;
+      }
+      last_sample_pdf = samp.pdf;
+      Vec3 wi_world = coord_po.to_world(samp.wi);
+      ray = Ray(po, wi_world);
+      ray.t_min = T_MIN_EPS / fmax_(std::fabs(samp.wi.z), 0.00001f);
+      throughput *= samp.bxdf * std::fabs(samp.wi.z) / fmax_(samp.pdf, 0.00001f);
+      if (!coord_po.in_expected_hemisphere(wi_world, samp.dir)) break;
+      if (dot(wi_world, inter.normal) < 0.0f) curr_medium = surf->inside_medium();
+    }
+    if (!throughput.is_finite()) break;
+    float rr_rand = rng.uniform_1d();
+    float rr_prop = clampf(throughput.luminance(), 0.001f, 0.95f);
+    if (rr_rand > rr_prop) break;
+    throughput /= rr_prop;
+    curr_depth += 1;
+  }
+  return final_color;
+}
+
+// ---- pixel_sampler/*.rs ---------------------------------------------------------------------------
+struct PixelSampler {
+  int kind = SPT_SAMPLER_RECURRENCE; uint32_t spp = 1, div_x = 1, div_y = 1;
+  uint32_t curr = 0; float cx = 0.5f, cy = 0.5f; // recurrence.rs:19-24 (state NOT reset per pixel, Q17)
+  uint32_t total() const { return kind == SPT_SAMPLER_JITTERED ? div_x * div_y : spp; }
+  void start_pixel() { curr = 0; }
+  bool next_sample(Rng& rng, float& ox, float& oy) {
+    if (curr >= total()) return false;
+    if (kind == SPT_SAMPLER_RECURRENCE) { // recurrence.rs:41-56
+      const float INV_PHI2 = 0.754877666246571f;
+      curr++;
+      cx += INV_PHI2; if (cx >= 1.0f) cx -= 1.0f;
+      cy += INV_PHI2 * INV_PHI2; if (cy >= 1.0f) cy -= 1.0f;
+      ox = cx; oy = cy;
+    } else if (kind == SPT_SAMPLER_RANDOM) { // random.rs:31-38
+      curr++; ox = rng.uniform_1d(); oy = rng.uniform_1d();
+    } else { // jittered.rs:44-57 (Q16: terminate after div_x*div_y)
+      uint32_t ix = curr % div_x, iy = curr / div_x;
+      ox = ((float)ix + rng.uniform_1d()) * (1.0f / (float)div_x);
+      oy = ((float)iy + rng.uniform_1d()) * (1.0f / (float)div_y);
+      curr++;
+    }
+    return true;
+  }
+};
+
+// Keyed-mode sub-pixel offset: the closed form the CUDA core uses (csrc/rng.cuh pixel_offset).
+inline void keyed_offset(const SptRenderDesc& r, uint64_t pixel, uint32_t k, Rng& rng, float& ox, float& oy) {
+  if (r.sampler_kind == SPT_SAMPLER_RECURRENCE) {
+    const uint32_t A1 = 3242174889u; // floor(0.754877666246571 * 2^32)
+    const uint32_t A2 = 2447445413u; // floor(0.754877666246571^2 * 2^32)
+    uint32_t n = (uint32_t)(pixel * (uint64_t)r.spp + k) + 1u;
+    uint32_t X = 0x80000000u + n * A1, Y = 0x80000000u + n * A2;
+    ox = (float)(X >> 8) * (1.0f / 16777216.0f); oy = (float)(Y >> 8) * (1.0f / 16777216.0f);
+  } else if (r.sampler_kind == SPT_SAMPLER_RANDOM) {
+    ox = rng.uniform_1d(); oy = rng.uniform_1d();
+  } else {
+    uint32_t ix = k % (uint32_t)r.div_x, iy = k / (uint32_t)r.div_x;
+    ox = ((float)ix + rng.uniform_1d()) * (1.0f / (float)r.div_x);
+    oy = ((float)iy + rng.uniform_1d()) * (1.0f / (float)r.div_y);
+  }
+}
+
+} // namespace
+
+// ---- PathTracer::render, pt.rs:237-295 ---------------------------------------------------------------
+// rng_mode 0: reference-faithful (one xoshiro stream + one sampler state per thread, contiguous row
+//             bands, n_threads = 2 x cores by default exactly like pt.rs:243-261);
+// rng_mode 1: keyed/paired (stream per (seed,pixel,sample) and closed-form sampler, same numbers as
+//             the CUDA core; rows are handed out dynamically since the result no longer depends on it).
+extern "C" int32_t orc_render(OrcScene* S, const SptRenderDesc* r, int32_t rng_mode, int32_t n_threads,
+                              float* out_rgb_mean, uint8_t* out_rgb8, SptStats* stats) {
+  if (!S || !r || !out_rgb_mean) { g_err = "null argument"; return SPT_ERR_INVALID; }
+  if (r->camera_index < 0 || r->camera_index >= (int)S->cameras.size()) { g_err = "bad camera index"; return SPT_ERR_INVALID; }
+  if (r->filter_radius > 0.5f) { g_err = "only box filter radius <= 0.5 supported"; return SPT_ERR_UNSUPPORTED; }
+  const int W = r->width, H = r->height;
+  const Camera& cam = S->cameras[r->camera_index];
+  const float aspect = (float)W / (float)H;
+  if (n_threads <= 0) n_threads = (int)std::thread::hardware_concurrency() * 2; // pt.rs:243
+  n_threads = std::max(1, std::min(n_threads, H));
+  PixelSampler proto; proto.kind = r->sampler_kind; proto.spp = (uint32_t)std::max(1, r->spp);
+  proto.div_x = (uint32_t)std::max(1, r->div_x); proto.div_y = (uint32_t)std::max(1, r->div_y);
+  const uint32_t spp = proto.total();
+  const float width_inv = 1.0f / (float)W, height_inv = 1.0f / (float)H;
+  const float spp_sqrt_inv = 1.0f / std::sqrt((float)spp);
+  std::vector<PathStats> tstats(n_threads);
+  std::vector<Counters> tcnt(n_threads);
+  std::atomic<int> next_row{0};
+  auto t_begin = std::chrono::steady_clock::now();
+
+  auto shade_pixel = [&](int i, int j, PixelSampler& ps, Rng& rng, PathStats& st) {
+    Color sum = BLACK; float weight_sum = 0.0f;
+    uint64_t pixel = (uint64_t)j * (uint64_t)W + (uint64_t)i;
+    ps.start_pixel();
+    for (uint32_t k = 0;; k++) {
+      float ox, oy;
+      if (rng_mode == 1) {
+        if (k >= spp) break;
+        rng.key(r->seed, pixel, k);
+        keyed_offset(*r, pixel, k, rng, ox, oy);
+      } else if (!ps.next_sample(rng, ox, oy)) break;
+      float x = (((float)i + ox) * width_inv - 0.5f) * aspect;            // pt.rs:269
+      float y = ((float)(H - j - 1) + oy) * height_inv - 0.5f;             // pt.rs:270-271
+      Ray ray = cam.generate_ray_with_aux_ray(x, y, aspect * width_inv * spp_sqrt_inv, height_inv * spp_sqrt_inv);
+      Color c = trace_ray(*S, ray, rng, r->max_depth, st);
+      if (!c.is_finite()) st.nonfinite++;
+      sum += c; weight_sum += 1.0f; // film.rs:82-87 with box r<=0.5: weight 1 per own-pixel sample
+    }
+    Color mean = sum / weight_sum; // film.rs:90
+    float* o = out_rgb_mean + 3 * pixel;
+    o[0] = mean.r; o[1] = mean.g; o[2] = mean.b;
+    if (out_rgb8) { // film.rs:94-99
+      uint8_t* q = out_rgb8 + 3 * pixel;
+      float v[3] = {mean.r, mean.g, mean.b};
+      for (int c2 = 0; c2 < 3; c2++) { float f = clampf(v[c2] * 255.0f, 0.0f, 255.0f); q[c2] = std::isnan(f) ? 0 : (uint8_t)f; }
+    }
+  };
+
+  std::vector<std::thread> threads;
+  for (int t = 0; t < n_threads; t++) {
+    threads.emplace_back([&, t] {
+      g_cnt = Counters();
+      PixelSampler ps = proto;
+      Rng rng = Rng::xoshiro(r->seed * 0x9E3779B97F4A7C15ull + (uint64_t)t + 1);
+      if (rng_mode == 0) { // renderer/util.rs:6-19
+        int per = H / n_threads;
+        int from = t * per, to = (t + 1 == n_threads) ? H : (t + 1) * per;
+        for (int j = from; j < to; j++) for (int i = 0; i < W; i++) shade_pixel(i, j, ps, rng, tstats[t]);
+      } else {
+        for (;;) { int j = next_row.fetch_add(1); if (j >= H) break; for (int i = 0; i < W; i++) shade_pixel(i, j, ps, rng, tstats[t]); }
+      }
+      tcnt[t] = g_cnt;
+    });
+  }
+  for (auto& th : threads) th.join();
+  double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
+  if (stats) {
+    memset(stats, 0, sizeof(*stats));
+    stats->paths = (uint64_t)W * H * spp;
+    for (int t = 0; t < n_threads; t++) {
+      stats->ext_rays += tstats[t].ext; stats->shadow_rays += tstats[t].shadow; stats->probe_rays += tstats[t].probe;
+      stats->nonfinite += tstats[t].nonfinite;
+      stats->nodes_visited += tcnt[t].nodes; stats->tris_tested += tcnt[t].prims; stats->insts_visited += tcnt[t].insts;
+    }
+    stats->seconds_total = secs;
+    stats->kernel_launches = 0;
+    stats->iterations = (uint64_t)n_threads; // reused: number of host threads
+  }
+  return SPT_OK;
+}
+
+// ---- seam B2 on ray batches ---------------------------------------------------------------------------
+static void parallel_for(int64_t n, int n_threads, const std::function<void(int64_t, int64_t, int)>& fn) {
+  if (n_threads <= 0) n_threads = (int)std::thread::hardware_concurrency();
+  n_threads = (int)std::max<int64_t>(1, std::min<int64_t>(n_threads, n));
+  std::vector<std::thread> th;
+  int64_t per = (n + n_threads - 1) / n_threads;
+  for (int t = 0; t < n_threads; t++) th.emplace_back([=, &fn] { fn(t * per, std::min(n, (t + 1) * per), t); });
+  for (auto& x : th) x.join();
+}
+
+static Ray to_ray(const SptRay& r) { Ray q(v3(r.origin), v3(r.direction)); q.t_min = r.t_min; return q; }
+
+extern "C" int32_t orc_trace_batch(OrcScene* S, const SptRay* rays, int64_t n, SptHit* out, int32_t n_threads, SptStats* stats) {
+  if (!S || !rays || !out) { g_err = "null argument"; return SPT_ERR_INVALID; }
+  std::vector<Counters> cnt(std::max(1, n_threads <= 0 ? (int)std::thread::hardware_concurrency() : n_threads));
+  parallel_for(n, n_threads, [&](int64_t a, int64_t b, int t) {
+    g_cnt = Counters();
+    for (int64_t i = a; i < b; i++) {
+      Ray q = to_ray(rays[i]);
+      Intersection inter = Intersection::with_t_max(rays[i].t_max);
+      SptHit h; h.t = rays[i].t_max; h.u = h.v = 0; h.prim_id = -1; h.inst_id = -1;
+      if (S->aggregate.intersect(q, inter)) {
+        h.t = inter.t; h.u = inter.bu; h.v = inter.bv;
+        h.prim_id = inter.primitive.kind == PrimRef::kTriangle ? inter.primitive.tri->tri_id : 0;
+        h.inst_id = inter.instance->inst_id;
+      }
+      out[i] = h;
+    }
+    cnt[t] = g_cnt;
+  });
+  if (stats) { memset(stats, 0, sizeof(*stats)); stats->ext_rays = (uint64_t)n;
+    for (auto& c : cnt) { stats->nodes_visited += c.nodes; stats->tris_tested += c.prims; stats->insts_visited += c.insts; } }
+  return SPT_OK;
+}
+
+extern "C" int32_t orc_occluded_batch(OrcScene* S, const SptRay* rays, int64_t n, uint8_t* out, int32_t n_threads) {
+  if (!S || !rays || !out) { g_err = "null argument"; return SPT_ERR_INVALID; }
+  parallel_for(n, n_threads, [&](int64_t a, int64_t b, int) {
+    for (int64_t i = a; i < b; i++) out[i] = S->aggregate.intersect_test(to_ray(rays[i]), rays[i].t_max) ? 1 : 0;
+  });
+  return SPT_OK;
+}
+
+// ---- BxDF test hook -------------------------------------------------------------------------------------
+extern "C" int32_t orc_bxdf_batch(OrcScene* S, const SptBxdfQuery* q, int64_t n, SptBxdfResult* out) {
+  if (!S || !q || !out) { g_err = "null argument"; return SPT_ERR_INVALID; }
+  for (int64_t i = 0; i < n; i++) {
+    if (q[i].material < 0 || q[i].material >= (int)S->materials.size()) { g_err = "bad material index"; return SPT_ERR_INVALID; }
+    Intersection inter; inter.texcoords = {q[i].texcoord[0], q[i].texcoord[1]};
+    Bxdf b = S->materials[q[i].material].bxdf_context(S->textures, inter);
+    Rng rng; rng.mode = Rng::kList; rng.list = q[i].rand; rng.list_n = 8; rng.list_i = 0;
+    BxdfInputs in; in.po = {0, 0, 0}; in.coord_po = Coordinate::from_tangent_normal({1, 0, 0}, {0, 0, 1}, {0, 0, 1});
+    in.wo = v3(q[i].wo); in.scene = nullptr;
+    SptBxdfResult r; memset(&r, 0, sizeof(r));
+    bool probe = b.sub.kind == Substrate::kSubsurface && (b.tag == Bxdf::kMicrofacetPlastic || b.tag == Bxdf::kSpecularPlastic);
+    (void)probe;
+    BxdfSample s = b.sample(in, rng);
+    r.sample_wi[0] = s.wi.x; r.sample_wi[1] = s.wi.y; r.sample_wi[2] = s.wi.z;
+    r.sample_f[0] = s.bxdf.r; r.sample_f[1] = s.bxdf.g; r.sample_f[2] = s.bxdf.b;
+    r.sample_pdf = s.pdf; r.sample_lobe = (int)s.lobe; r.sample_dir = (int)s.dir; r.n_rand_used = rng.list_i;
+    Vec3 wi = v3(q[i].wi);
+    Color f = b.bxdf(in.wo, wi);
+    r.eval_f[0] = f.r; r.eval_f[1] = f.g; r.eval_f[2] = f.b; r.eval_pdf = b.pdf(in.wo, wi);
+    r.is_delta = b.is_delta(); r.bxdf_tag = (int)b.tag;
+    out[i] = r;
+  }
+  return SPT_OK;
+}
+
+// ---- small hooks for the known-answer tests -------------------------------------------------------------
+extern "C" int32_t orc_alias_table(const float* props, int32_t n, float* u_out, int64_t* k_out) {
+  AliasTable a; a.build(std::vector<float>(props, props + n));
+  for (int i = 0; i < n; i++) { u_out[i] = a.u[i]; k_out[i] = (int64_t)a.k[i]; }
+  return SPT_OK;
+}
+extern "C" int32_t orc_alias_sample(const float* props, int32_t n, const float* rand, int64_t m, int64_t* idx_out) {
+  AliasTable a; a.build(std::vector<float>(props, props + n));
+  for (int64_t i = 0; i < m; i++) { float p; idx_out[i] = (int64_t)a.sample(rand[i], p); }
+  return SPT_OK;
+}
+// light sampler probabilities (power_is alias props / uniform 1/n) in light order
+extern "C" int32_t orc_light_probs(OrcScene* S, float* out) {
+  const LightSampler& ls = S->light_sampler;
+  for (size_t i = 0; i < ls.lights.size(); i++) out[i] = ls.kind == 1 ? ls.alias.probability(i) : ls.num_light_inv;
+  return SPT_OK;
+}
+extern "C" int32_t orc_rng_stream(uint64_t seed, uint64_t pixel, uint64_t sample, int32_t n, float* out) {
+  Rng r; r.key(seed, pixel, sample);
+  for (int i = 0; i < n; i++) out[i] = r.uniform_1d();
+  return SPT_OK;
+}
