@@ -13,6 +13,15 @@ namespace orc {
 
 struct Counters { uint64_t nodes = 0, prims = 0, insts = 0; };
 inline thread_local Counters g_cnt;
+// Oracle-only switches (both default to the reference's behaviour):
+//  g_fix_q1          build the BVH with the evidently intended bucket rule (centroid relative to the NODE box).
+//                    Hits are topology-independent (except exact-t ties), so this only makes the checker fast
+//                    enough for high-spp image comparisons; never used for the timed CPU baseline.
+//  g_file_order_pick BvhAccel::sample picks primitives in file order instead of BVH order (a permutation of a
+//                    uniform pick).  Set in keyed/paired RNG mode so the CUDA core, whose BVH differs, draws the
+//                    same triangle from the same random number.
+inline bool g_fix_q1 = false;
+inline thread_local bool g_file_order_pick = false;
 
 struct AuxRay { Vec3 x_origin, x_direction, y_origin, y_direction; }; // ray.rs:9-15
 struct Ray {                                                          // ray.rs:1-7
@@ -152,6 +161,7 @@ struct BvhAccel {
   struct Node { int lc = -1, rc = -1; Bbox bbox; size_t start = 0, end = 0; size_t size() const { return end - start; } bool is_leaf() const { return lc < 0; } };
   std::vector<Node> nodes; // nodes[0] = root (empty vector = no root)
   std::vector<const P*> primitives;
+  std::vector<const P*> file_order; // oracle-only, see g_file_order_pick
 
   static void find_best_split(const std::vector<Bbox>& boxes, const std::vector<std::vector<size_t>>& idx,
                               size_t total, size_t nb, float& best_cost, size_t& best_split) { // :143-174
@@ -171,6 +181,7 @@ struct BvhAccel {
 
   void build(std::vector<const P*> prims, size_t max_leaf, size_t nb) { // BvhAccel::new, :23-141
     primitives = std::move(prims);
+    file_order = primitives;
     nodes.clear();
     if (primitives.empty()) return;
     Bbox bbox = primitives[0]->bbox();
@@ -188,11 +199,15 @@ struct BvhAccel {
       for (size_t i = ustart; i < uend; i++) {
         Bbox pb = primitives[i]->bbox(); // shadows the node bbox: Q1 (bvh.rs:55-58)
         Vec3 c = pb.centroid();
-        float x = (c.x - pb.p_min.x) / len.x;
+        Vec3 ref_min = g_fix_q1 ? ub.p_min : pb.p_min;
+        float x = (c.x - ref_min.x) / len.x;
+        if (g_fix_q1 && x >= (float)nb) x = (float)(nb - 1); // centroid on the node's max face
         if (x >= 0.0f && x < (float)nb) { size_t k = (size_t)x; bx[k] = bx[k].merge(pb); ix[k].push_back(i); }
-        float y = (c.y - pb.p_min.y) / len.y;
+        float y = (c.y - ref_min.y) / len.y;
+        if (g_fix_q1 && y >= (float)nb) y = (float)(nb - 1); // centroid on the node's max face
         if (y >= 0.0f && y < (float)nb) { size_t k = (size_t)y; by[k] = by[k].merge(pb); iy[k].push_back(i); }
-        float z = (c.z - pb.p_min.z) / len.z;
+        float z = (c.z - ref_min.z) / len.z;
+        if (g_fix_q1 && z >= (float)nb) z = (float)(nb - 1); // centroid on the node's max face
         if (z >= 0.0f && z < (float)nb) { size_t k = (size_t)z; bz[k] = bz[k].merge(pb); iz[k].push_back(i); }
       }
       float cx = FLT_MAX, cy = FLT_MAX, cz = FLT_MAX;
@@ -261,7 +276,7 @@ struct BvhAccel {
   Intersection sample(Rng& rng, float& pdf) const { // :293-298
     float fi = rng.uniform_1d() * (float)primitives.size();
     size_t index = std::min((size_t)fi, primitives.size() - 1);
-    Intersection inter = primitives[index]->sample(rng, pdf);
+    Intersection inter = (g_file_order_pick ? file_order[index] : primitives[index])->sample(rng, pdf);
     pdf = pdf / (float)primitives.size();
     return inter;
   }

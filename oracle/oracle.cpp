@@ -164,6 +164,7 @@ extern "C" int32_t orc_scene_create(const SptSceneDesc* d, OrcScene** out) {
 }
 
 extern "C" void orc_scene_destroy(OrcScene* s) { delete s; }
+extern "C" void orc_set_fix_q1(int32_t on) { g_fix_q1 = on != 0; } // affects scenes created afterwards
 
 // ---- renderer/pt.rs -------------------------------------------------------------------------------
 namespace {
@@ -395,6 +396,7 @@ extern "C" int32_t orc_render(OrcScene* S, const SptRenderDesc* r, int32_t rng_m
   for (int t = 0; t < n_threads; t++) {
     threads.emplace_back([&, t] {
       g_cnt = Counters();
+      g_file_order_pick = (rng_mode == 1);
       PixelSampler ps = proto;
       Rng rng = Rng::xoshiro(r->seed * 0x9E3779B97F4A7C15ull + (uint64_t)t + 1);
       if (rng_mode == 0) { // renderer/util.rs:6-19

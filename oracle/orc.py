@@ -34,6 +34,8 @@ def lib():
         L.orc_scene_create.argtypes = [C.POINTER(abi.SceneDesc), C.POINTER(vp)]
         L.orc_scene_destroy.argtypes = [vp]
         L.orc_scene_destroy.restype = None
+        L.orc_set_fix_q1.argtypes = [C.c_int32]
+        L.orc_set_fix_q1.restype = None
         L.orc_render.argtypes = [vp, C.POINTER(abi.RenderDesc), C.c_int32, C.c_int32, vp, vp, C.POINTER(abi.Stats)]
         L.orc_trace_batch.argtypes = [vp, vp, C.c_int64, vp, C.c_int32, C.POINTER(abi.Stats)]
         L.orc_occluded_batch.argtypes = [vp, vp, C.c_int64, vp, C.c_int32]
@@ -56,11 +58,14 @@ HIT_DT = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim_id", "<i4"),
 
 
 class OracleScene:
-    def __init__(self, flat_scene):
+    def __init__(self, flat_scene, fix_q1=False):
+        """fix_q1=True builds the checker's BVH with the intended bucket rule (fast; same hits up to exact ties)."""
         self.fs = flat_scene
+        lib().orc_set_fix_q1(1 if fix_q1 else 0)
         self._desc = flat_scene.to_desc()
         self.h = C.c_void_p()
         _chk(lib().orc_scene_create(C.byref(self._desc), C.byref(self.h)))
+        lib().orc_set_fix_q1(0)
 
     def close(self):
         if self.h:

@@ -1,0 +1,358 @@
+// flatten.cpp — SptSceneDesc -> device-layout arrays.  Runs once per scene on the host and replaces the
+// constructors the reference runs while loading: Instance::new (instance.rs:19-29), TriMesh::new + BvhAccel::new
+// (triangle.rs:42-55, bvh.rs:23-141; tree rebuilt as a compressed wide BVH), generate_mipmap (image_tex.rs:63-98),
+// EnvLight::new (environment.rs:18-50), AliasTable::new (alias_table.rs:8-56), PowerIsLightSampler::new
+// (power_is.rs:19-42) with LightT::power (shape_light.rs:78-81, sphere.rs:122-135, triangle.rs:282-288).
+#include "flatten.h"
+#include <cmath>
+#include <cstring>
+#include <cfloat>
+#include <algorithm>
+
+namespace spt {
+namespace {
+
+struct V3 { float x, y, z; };
+inline V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+inline V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline V3 operator*(V3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+inline V3 neg(V3 a) { return {-a.x, -a.y, -a.z}; }
+inline float dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+inline V3 cross(V3 a, V3 b) { return {a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y}; }
+inline float length(V3 a) { return std::sqrt(dot(a, a)); }
+struct M3 { V3 cx, cy, cz; };                        // column vectors (glam Mat3A)
+inline V3 mul(const M3& m, V3 v) { return (m.cx * v.x + m.cy * v.y) + m.cz * v.z; }
+inline M3 mul(const M3& a, const M3& b) { return {mul(a, b.cx), mul(a, b.cy), mul(a, b.cz)}; }
+inline M3 transpose(const M3& m) { return {{m.cx.x, m.cy.x, m.cz.x}, {m.cx.y, m.cy.y, m.cz.y}, {m.cx.z, m.cy.z, m.cz.z}}; }
+inline M3 inverse(const M3& m) { // glam Mat3A::inverse
+  V3 t0 = cross(m.cy, m.cz), t1 = cross(m.cz, m.cx), t2 = cross(m.cx, m.cy);
+  float inv = 1.0f / dot(m.cz, t2);
+  return transpose(M3{t0 * inv, t1 * inv, t2 * inv});
+}
+struct A3 { M3 m; V3 t; };
+inline A3 inverse(const A3& a) { M3 mi = inverse(a.m); return {mi, neg(mul(mi, a.t))}; }
+inline V3 point(const A3& a, V3 p) { return mul(a.m, p) + a.t; }
+inline float lum(const float* c) { return 0.299f * c[0] + 0.587f * c[1] + 0.114f * c[2]; }
+inline float4 row(const M3& m, int i, float w) {
+  const float* x = &m.cx.x; const float* y = &m.cy.x; const float* z = &m.cz.x;
+  return make_float4(x[i], y[i], z[i], w);
+}
+
+// AliasTable::new, alias_table.rs:8-56 (the author's own pairing, not Vose); returns (u, k)
+void alias_build(const std::vector<float>& props, std::vector<float2>& out) {
+  const size_t n = props.size();
+  std::vector<float> u(n); std::vector<size_t> k(n);
+  for (size_t i = 0; i < n; i++) { u[i] = props[i] * (float)n; k[i] = i; }
+  long poor = -1, rich = -1;
+  for (size_t i = 0; i < n; i++) if (u[i] < 1.0f) { poor = (long)i; break; }
+  long poor_max = poor;
+  for (size_t i = 0; i < n; i++) if (u[i] > 1.0f) { rich = (long)i; break; }
+  while (poor >= 0 && rich >= 0) {
+    u[rich] -= 1.0f - u[poor];
+    k[poor] = (size_t)rich;
+    if (u[rich] < 1.0f && rich < poor_max) poor = rich;
+    else {
+      poor = -1;
+      for (size_t i = (size_t)poor_max + 1; i < n; i++) if (u[i] < 1.0f) { poor = (long)i; poor_max = (long)i; break; }
+    }
+    const long r0 = rich; rich = -1;
+    for (size_t i = (size_t)r0; i < n; i++) if (u[i] > 1.0f) { rich = (long)i; break; }
+  }
+  out.resize(n);
+  for (size_t i = 0; i < n; i++) { int32_t ki = (int32_t)k[i]; float kf; memcpy(&kf, &ki, 4); out[i] = make_float2(u[i], kf); }
+}
+
+inline float srgb_lin(float s) { return s <= 0.04045f ? s / 12.92f : std::pow((s + 0.055f) / 1.055f, 2.4f); }
+
+// TextureT::average_color (scalar.rs:35-37, image_tex.rs:41-44, binary_op.rs:59-61, srgb_tex.rs:30-32, input_modifier.rs:78-80)
+void tex_average(const HostScene& hs, int id, float out[3]) {
+  const DTexture& t = hs.textures[id];
+  float a[3], b[3];
+  switch (t.tag) {
+    case SPT_TEX_SCALAR: out[0] = t.value[0]; out[1] = t.value[1]; out[2] = t.value[2]; return;
+    case SPT_TEX_IMAGE: {
+      const DMip& m = hs.mips[t.mip_base + t.n_mips - 1];
+      const uchar4 p = hs.texels[m.texel_base];
+      out[0] = p.x / 255.0f; out[1] = p.y / 255.0f; out[2] = p.z / 255.0f; return;
+    }
+    case SPT_TEX_ADD: case SPT_TEX_SUB: case SPT_TEX_MUL: case SPT_TEX_DIV:
+      tex_average(hs, t.child0, a); tex_average(hs, t.child1, b);
+      for (int c = 0; c < 3; c++) out[c] = t.tag == SPT_TEX_ADD ? a[c] + b[c] : t.tag == SPT_TEX_SUB ? a[c] - b[c] : t.tag == SPT_TEX_MUL ? a[c] * b[c] : a[c] / b[c];
+      return;
+    case SPT_TEX_SRGB: tex_average(hs, t.child0, a); for (int c = 0; c < 3; c++) out[c] = srgb_lin(a[c]); return;
+    default: tex_average(hs, t.child0, out); return;
+  }
+}
+
+} // namespace
+
+std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
+  auto bad = [](const char* m) { return std::string(m); };
+  if (d.n_cameras <= 0) return bad("At least one camera is needed");
+  // ---- textures (+ mip pyramids) -----------------------------------------------------------------------------
+  hs.textures.resize(d.n_textures);
+  for (int i = 0; i < d.n_textures; i++) {
+    const SptTextureDesc& t = d.textures[i];
+    DTexture o; memset(&o, 0, sizeof(o));
+    o.tag = t.tag; o.child0 = t.child[0]; o.child1 = t.child[1]; o.mode = t.mode; o.wrap = t.wrap;
+    for (int c = 0; c < 3; c++) { o.value[c] = t.value[c]; o.tiling[c] = t.tiling[c]; o.offset[c] = t.offset[c]; }
+    if (t.tag < 0 || t.tag > SPT_TEX_INPUT_MODIFIER) return bad("texture: unknown tag");
+    if (t.tag >= SPT_TEX_ADD && (t.child[0] < 0 || t.child[0] >= i)) return bad("texture: child must precede its parent");
+    if (t.tag >= SPT_TEX_ADD && t.tag <= SPT_TEX_DIV && (t.child[1] < 0 || t.child[1] >= i)) return bad("texture: child must precede its parent");
+    if (t.tag == SPT_TEX_IMAGE) {
+      if (!t.rgba || t.width <= 0 || t.height <= 0) return bad("image texture without pixels");
+      hs.has_image_tex = true;
+      o.mip_base = (int32_t)hs.mips.size();
+      int w = t.width, h = t.height;
+      std::vector<uchar4> cur((size_t)w * h);
+      memcpy(cur.data(), t.rgba, (size_t)4 * w * h);
+      for (;;) {
+        DMip m; m.w = w; m.h = h; m.texel_base = (uint32_t)hs.texels.size(); m.pad = 0;
+        hs.mips.push_back(m);
+        hs.texels.insert(hs.texels.end(), cur.begin(), cur.end());
+        o.n_mips++;
+        if (!(w > 1 || h > 1)) break;
+        const int nw = (w + 1) >> 1, nh = (h + 1) >> 1; // generate_mipmap: box filter through u8 truncation
+        std::vector<uchar4> nxt((size_t)nw * nh);
+        for (int x = 0; x < nw; x++) for (int y = 0; y < nh; y++) {
+          const int x0 = 2 * x, x1 = std::min(2 * x + 1, w - 1), y0 = 2 * y, y1 = std::min(2 * y + 1, h - 1);
+          const uchar4 p0 = cur[(size_t)y0 * w + x0], p1 = cur[(size_t)y1 * w + x0], p2 = cur[(size_t)y0 * w + x1], p3 = cur[(size_t)y1 * w + x1];
+          uchar4 q;
+          q.x = (unsigned char)(((float)p0.x + (float)p1.x + (float)p2.x + (float)p3.x) * 0.25f);
+          q.y = (unsigned char)(((float)p0.y + (float)p1.y + (float)p2.y + (float)p3.y) * 0.25f);
+          q.z = (unsigned char)(((float)p0.z + (float)p1.z + (float)p2.z + (float)p3.z) * 0.25f);
+          q.w = (unsigned char)(((float)p0.w + (float)p1.w + (float)p2.w + (float)p3.w) * 0.25f);
+          nxt[(size_t)y * nw + x] = q;
+        }
+        cur.swap(nxt); w = nw; h = nh;
+      }
+    }
+    hs.textures[i] = o;
+  }
+  auto tex_ok = [&](int id) { return id >= 0 && id < d.n_textures; };
+  // ---- materials / mediums / surfaces ---------------------------------------------------------------------------
+  hs.materials.resize(d.n_materials);
+  for (int i = 0; i < d.n_materials; i++) {
+    const SptMaterialDesc& m = d.materials[i];
+    if (m.tag < 0 || m.tag > SPT_MAT_SUBSURFACE) return bad("material: unknown tag");
+    DMaterial o; o.tag = m.tag; o.ior = m.ior; o.rough_chan = m.rough_chan; o.metal_chan = m.metal_chan;
+    for (int k = 0; k < 4; k++) o.tex[k] = m.tex[k];
+    const bool need[8][4] = {{1, 0, 0, 0}, {0, 0, 0, 0}, {1, 1, 1, 1}, {0, 0, 1, 1}, {1, 0, 1, 1}, {1, 1, 1, 1}, {1, 1, 1, 1}, {1, 1, 1, 1}};
+    for (int k = 0; k < 4; k++) if (need[m.tag][k] && !tex_ok(m.tex[k])) return bad("material: bad texture index");
+    hs.materials[i] = o;
+  }
+  hs.mediums.resize(d.n_mediums);
+  for (int i = 0; i < d.n_mediums; i++) { // Homogeneous::new, homogeneous.rs:12-19
+    DMedium o; memset(&o, 0, sizeof(o));
+    for (int c = 0; c < 3; c++) { o.sigma_t[c] = d.mediums[i].sigma_a[c] + d.mediums[i].sigma_s[c]; o.sigma_s[c] = d.mediums[i].sigma_s[c]; }
+    o.g = d.mediums[i].asymmetric;
+    hs.mediums[i] = o;
+  }
+  hs.surfaces.resize(d.n_surfaces);
+  for (int i = 0; i < d.n_surfaces; i++) {
+    const SptSurfaceDesc& s = d.surfaces[i];
+    if (s.material < 0 || s.material >= d.n_materials) return bad("surface: bad material index");
+    if ((s.normal_map >= 0 && !tex_ok(s.normal_map)) || (s.emissive_map >= 0 && !tex_ok(s.emissive_map))) return bad("surface: bad texture index");
+    if (s.inside_medium >= d.n_mediums) return bad("surface: bad medium index");
+    DSurface o; o.material = s.material; o.normal_map = s.normal_map; o.emissive_map = s.emissive_map;
+    o.double_sided = s.double_sided; o.inside_medium = s.inside_medium;
+    for (int c = 0; c < 3; c++) o.emissive[c] = s.emissive[c];
+    hs.surfaces[i] = o;
+  }
+  // ---- spheres, meshes (+ BLAS) ------------------------------------------------------------------------------------
+  hs.spheres.resize(d.n_spheres);
+  for (int i = 0; i < d.n_spheres; i++) hs.spheres[i] = make_float4(d.spheres[i].center[0], d.spheres[i].center[1], d.spheres[i].center[2], d.spheres[i].radius);
+  // reserve node 0.. for the TLAS: build BLASes into a temporary list first, then lay out TLAS | BLAS...
+  std::vector<std::vector<CwNode>> blas_nodes(d.n_meshes);
+  std::vector<Box3> mesh_box(d.n_meshes);
+  hs.meshes.resize(d.n_meshes);
+  std::vector<std::vector<int>> blas_order(d.n_meshes);
+  for (int mi = 0; mi < d.n_meshes; mi++) {
+    const SptMeshDesc& m = d.meshes[mi];
+    if (m.n_tris <= 0 || m.n_verts <= 0 || !m.position || !m.index) return bad("mesh: empty");
+    DMesh dm; dm.vert_base = (int32_t)(hs.verts.size() / 4); dm.idx_base = (int32_t)(hs.indices.size() / 3); dm.n_tris = m.n_tris; dm.blas_root = 0;
+    for (int v = 0; v < m.n_verts; v++) {
+      const float* p = m.position + 3 * v;
+      const float nz[3] = {0, 0, 1}, tx[3] = {1, 0, 0}, by[3] = {0, 1, 0}, uv0[2] = {0, 0};
+      const float* n = m.normal ? m.normal + 3 * v : nz; const float* uv = m.texcoord ? m.texcoord + 2 * v : uv0;
+      const float* t = m.tangent ? m.tangent + 3 * v : tx; const float* b = m.bitangent ? m.bitangent + 3 * v : by;
+      hs.verts.push_back(make_float4(p[0], p[1], p[2], uv[0]));
+      hs.verts.push_back(make_float4(n[0], n[1], n[2], uv[1]));
+      hs.verts.push_back(make_float4(t[0], t[1], t[2], 0.f));
+      hs.verts.push_back(make_float4(b[0], b[1], b[2], 0.f));
+    }
+    std::vector<Box3> boxes(m.n_tris);
+    for (int t = 0; t < m.n_tris; t++) {
+      Box3 bx; for (int k = 0; k < 3; k++) { bx.lo[k] = FLT_MAX; bx.hi[k] = -FLT_MAX; }
+      for (int c = 0; c < 3; c++) {
+        const uint32_t vi = m.index[3 * t + c];
+        if (vi >= (uint32_t)m.n_verts) return bad("mesh: vertex index out of range");
+        hs.indices.push_back(vi);
+        for (int k = 0; k < 3; k++) { bx.lo[k] = std::min(bx.lo[k], m.position[3 * vi + k]); bx.hi[k] = std::max(bx.hi[k], m.position[3 * vi + k]); }
+      }
+      boxes[t] = bx;
+    }
+    hs.meshes[mi] = dm;
+    // node/prim bases are patched below once the TLAS size is known: build with base 0 and offset afterwards
+    build_cwbvh(boxes, 3, 0, 0, blas_nodes[mi], blas_order[mi], &mesh_box[mi]);
+  }
+  // ---- instances ------------------------------------------------------------------------------------------------------
+  hs.inst.resize(d.n_instances); hs.inst_shade.resize(d.n_instances);
+  std::vector<Box3> inst_box(d.n_instances);
+  std::vector<A3> inst_fwd(d.n_instances);
+  for (int i = 0; i < d.n_instances; i++) {
+    const SptInstanceDesc& in = d.instances[i];
+    if (in.surface < 0 || in.surface >= d.n_surfaces) return bad("instance: bad surface index");
+    const float* x = in.xform;
+    A3 a{{{x[0], x[1], x[2]}, {x[3], x[4], x[5]}, {x[6], x[7], x[8]}}, {x[9], x[10], x[11]}};
+    const A3 ai = inverse(a);
+    const M3 it = transpose(ai.m); // Transform::new, transform.rs:18-22
+    DInstance o;
+    o.inv0 = row(ai.m, 0, ai.t.x); o.inv1 = row(ai.m, 1, ai.t.y); o.inv2 = row(ai.m, 2, ai.t.z);
+    o.kind = in.prim_kind; o.surface = in.surface; o.mesh = -1; o.root = 0;
+    Box3 pb;
+    if (in.prim_kind == SPT_PRIM_SPHERE) {
+      if (in.prim_index < 0 || in.prim_index >= d.n_spheres) return bad("instance: bad sphere index");
+      o.root = in.prim_index;
+      const float4 s = hs.spheres[in.prim_index];
+      pb.lo[0] = s.x - s.w; pb.lo[1] = s.y - s.w; pb.lo[2] = s.z - s.w; pb.hi[0] = s.x + s.w; pb.hi[1] = s.y + s.w; pb.hi[2] = s.z + s.w;
+    } else if (in.prim_kind == SPT_PRIM_TRIMESH) {
+      if (in.prim_index < 0 || in.prim_index >= d.n_meshes) return bad("instance: bad mesh index");
+      o.mesh = in.prim_index; pb = mesh_box[in.prim_index];
+    } else return bad("instance: unknown primitive kind");
+    Box3 wb; for (int k = 0; k < 3; k++) { wb.lo[k] = FLT_MAX; wb.hi[k] = -FLT_MAX; }
+    for (int c = 0; c < 8; c++) { // Bbox::transformed_by, bbox.rs:41-61
+      const V3 p = point(a, V3{(c & 4) ? pb.hi[0] : pb.lo[0], (c & 2) ? pb.hi[1] : pb.lo[1], (c & 1) ? pb.hi[2] : pb.lo[2]});
+      wb.lo[0] = std::min(wb.lo[0], p.x); wb.lo[1] = std::min(wb.lo[1], p.y); wb.lo[2] = std::min(wb.lo[2], p.z);
+      wb.hi[0] = std::max(wb.hi[0], p.x); wb.hi[1] = std::max(wb.hi[1], p.y); wb.hi[2] = std::max(wb.hi[2], p.z);
+    }
+    inst_box[i] = wb; inst_fwd[i] = a;
+    DInstanceShade sh;
+    sh.fwd0 = row(a.m, 0, a.t.x); sh.fwd1 = row(a.m, 1, a.t.y); sh.fwd2 = row(a.m, 2, a.t.z);
+    sh.it0 = row(it, 0, 0.f); sh.it1 = row(it, 1, 0.f); sh.it2 = row(it, 2, 0.f);
+    hs.inst[i] = o; hs.inst_shade[i] = sh;
+  }
+  // ---- TLAS, then lay the BLASes out behind it ---------------------------------------------------------------------------
+  std::vector<CwNode> tlas; std::vector<int> tlas_order;
+  build_cwbvh(inst_box, 1, 0, 0, tlas, tlas_order, nullptr);
+  hs.nodes = tlas; hs.tlas_nodes = (int64_t)tlas.size();
+  hs.tlas_inst.assign(tlas_order.begin(), tlas_order.end());
+  for (int mi = 0; mi < d.n_meshes; mi++) {
+    const uint32_t node_base = (uint32_t)hs.nodes.size(), tri_base = (uint32_t)(hs.tris.size() / 3);
+    hs.meshes[mi].blas_root = (int32_t)node_base;
+    for (CwNode n : blas_nodes[mi]) { n.child_base += node_base; n.prim_base += tri_base; hs.nodes.push_back(n); }
+    const SptMeshDesc& m = d.meshes[mi];
+    for (int t : blas_order[mi]) {
+      float idf; int32_t id = t; memcpy(&idf, &id, 4);
+      for (int c = 0; c < 3; c++) { const float* p = m.position + 3 * m.index[3 * t + c]; hs.tris.push_back(make_float4(p[0], p[1], p[2], c == 0 ? idf : 0.f)); }
+    }
+    hs.blas_nodes += (int64_t)blas_nodes[mi].size();
+  }
+  for (int i = 0; i < d.n_instances; i++) if (hs.inst[i].kind == SPT_PRIM_TRIMESH) hs.inst[i].root = hs.meshes[hs.inst[i].mesh].blas_root;
+  // ---- environment -----------------------------------------------------------------------------------------------------------
+  float env_avg_power = 0.f;
+  if (d.env) { // EnvLight::new, environment.rs:18-50 (Q7: theta lacks the factor pi)
+    const int W = d.env->width, H = d.env->height;
+    if (W <= 0 || H <= 0 || !d.env->rgb) return bad("environment: empty");
+    hs.env_w = W; hs.env_h = H;
+    for (int c = 0; c < 3; c++) hs.env_scale[c] = d.env->scale[c];
+    std::vector<float> props((size_t)W * H);
+    float sum = 0.0f; const float hinv = 1.0f / (float)H;
+    for (int y = 0; y < H; y++) for (int x = 0; x < W; x++) {
+      const float theta = ((float)y + 0.5f) * hinv;
+      const float p = lum(d.env->rgb + 3 * ((size_t)y * W + x)) * std::sin(theta);
+      sum += p; props[(size_t)y * W + x] = p;
+    }
+    const float sinv = 1.0f / sum;
+    for (auto& p : props) p *= sinv;
+    hs.env_tex.resize(props.size());
+    for (size_t i = 0; i < props.size(); i++) hs.env_tex[i] = make_float4(d.env->rgb[3 * i], d.env->rgb[3 * i + 1], d.env->rgb[3 * i + 2], props[i]);
+    alias_build(props, hs.env_alias);
+    env_avg_power = sum / (float)props.size(); // environment.rs:39; power = avg_power * 4 pi (:139-141)
+  }
+  // ---- lights + light sampler ----------------------------------------------------------------------------------------------------
+  hs.light_sampler = d.light_sampler; hs.env_light_index = d.env_light_index;
+  hs.inst_light.assign(std::max(1, d.n_instances), -1);
+  hs.lights.resize(d.n_lights);
+  std::vector<float> power(d.n_lights, 0.f);
+  for (int i = 0; i < d.n_lights; i++) {
+    const SptLightDesc& l = d.lights[i];
+    DLight o; memset(&o, 0, sizeof(o));
+    o.tag = l.tag; o.instance = l.instance;
+    for (int c = 0; c < 3; c++) { o.position[c] = l.position[c]; o.direction[c] = l.direction[c]; o.strength[c] = l.strength[c]; }
+    o.cos_inner = std::cos(l.inner_angle); o.cos_outer = std::cos(l.outer_angle); // SpotLight::new, spot.rs:22-23
+    switch (l.tag) {
+      case SPT_LIGHT_DIRECTIONAL: { // DirLight::new normalises, directional.rs:11-16
+        V3 dn{l.direction[0], l.direction[1], l.direction[2]}; const float len = length(dn);
+        o.direction[0] = dn.x / len; o.direction[1] = dn.y / len; o.direction[2] = dn.z / len;
+        power[i] = lum(l.strength); break;
+      }
+      case SPT_LIGHT_POINT: case SPT_LIGHT_SPOT: power[i] = lum(l.strength); break;
+      case SPT_LIGHT_SHAPE: {
+        if (l.instance < 0 || l.instance >= d.n_instances) return bad("shape light: bad instance index");
+        hs.inst_light[l.instance] = i;
+        const SptInstanceDesc& in = d.instances[l.instance];
+        const A3& a = inst_fwd[l.instance];
+        float area = 0.f;
+        if (in.prim_kind == SPT_PRIM_SPHERE) { // Sphere::surface_area, sphere.rs:122-135
+          const float r = d.spheres[in.prim_index].radius * 0.5f;
+          const V3 v0 = mul(a.m, V3{-r, -r, -r}), v1 = mul(a.m, V3{-r, -r, r}), v2 = mul(a.m, V3{-r, r, -r}), v3 = mul(a.m, V3{r, -r, -r});
+          const float a2 = dot(v0 - v1, v0 - v1), b2 = dot(v0 - v2, v0 - v2), c2 = dot(v0 - v3, v0 - v3);
+          area = 4.0f * 3.14159265358979323846f * std::sqrt((a2 * b2 + b2 * c2 + c2 * a2) / 3.0f);
+        } else { // sum of Triangle::surface_area, triangle.rs:282-288
+          const SptMeshDesc& m = d.meshes[in.prim_index];
+          for (int t = 0; t < m.n_tris; t++) {
+            V3 p[3];
+            for (int c = 0; c < 3; c++) { const float* q = m.position + 3 * m.index[3 * t + c]; p[c] = point(a, V3{q[0], q[1], q[2]}); }
+            area += length(cross(p[1] - p[0], p[2] - p[0])) * 0.5f;
+          }
+        }
+        const SptSurfaceDesc& sf = d.surfaces[in.surface];
+        float e[3] = {sf.emissive[0], sf.emissive[1], sf.emissive[2]};
+        if (sf.emissive_map >= 0) { float av[3]; tex_average(hs, sf.emissive_map, av); for (int c = 0; c < 3; c++) e[c] *= av[c]; }
+        power[i] = area * lum(e);
+        break;
+      }
+      case SPT_LIGHT_ENV:
+        if (!d.env) return bad("env light without environment");
+        power[i] = env_avg_power * 4.0f * 3.14159265358979323846f; break;
+      default: return bad("light: unknown tag");
+    }
+    hs.lights[i] = o;
+  }
+  hs.light_prob.assign(std::max(1, d.n_lights), 0.f);
+  hs.light_alias.assign(std::max(1, d.n_lights), make_float2(1.f, 0.f));
+  if (d.light_sampler == SPT_LS_POWER_IS && d.n_lights > 0) { // power_is.rs:24-34
+    float sum = 0.f;
+    for (float p : power) sum += p;
+    const float sinv = 1.0f / sum;
+    std::vector<float> props(d.n_lights);
+    for (int i = 0; i < d.n_lights; i++) props[i] = power[i] * sinv;
+    hs.light_prob = props;
+    alias_build(props, hs.light_alias);
+  }
+  // ---- SS_CDF_TABLE, substrate.rs:187-196 ---------------------------------------------------------------------------------------------
+  hs.ss_cdf.resize(1024);
+  for (int i = 0; i < 512; i++) {
+    float x = (float)i / 512.0f;
+    x = -2.0f * std::log(1.0f - x);
+    hs.ss_cdf[2 * i] = x;
+    hs.ss_cdf[2 * i + 1] = 1.0f - std::exp(-x) * 0.25f - std::exp(-x / 3.0f) * 0.75f;
+  }
+  // ---- cameras, PerspectiveCamera::new (perspective.rs:15-27) ---------------------------------------------------------------------------
+  hs.cameras.resize(d.n_cameras);
+  for (int i = 0; i < d.n_cameras; i++) {
+    const SptCameraDesc& c = d.cameras[i];
+    V3 f{c.forward[0], c.forward[1], c.forward[2]}, u{c.up[0], c.up[1], c.up[2]};
+    const float fl = length(f); f = {f.x / fl, f.y / fl, f.z / fl};
+    V3 r = cross(f, u); const float rl = length(r); r = {r.x / rl, r.y / rl, r.z / rl};
+    u = cross(r, f);
+    DCamera o;
+    for (int k = 0; k < 3; k++) { o.eye[k] = c.eye[k]; o.forward[k] = (&f.x)[k]; o.right[k] = (&r.x)[k]; o.up[k] = (&u.x)[k]; }
+    o.half_cot_half_fov = 0.5f / std::tan(c.fov * 0.5f);
+    hs.cameras[i] = o;
+  }
+  return std::string();
+}
+
+} // namespace spt

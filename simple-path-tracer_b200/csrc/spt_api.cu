@@ -1,0 +1,385 @@
+// spt_api.cu — the extern "C" entry points of include/spt.h: context, scene upload, ray batches, render loop.
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <algorithm>
+#include <new>
+#include "../../include/spt.h"
+#include "flatten.h"
+#include "kernels.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+int fail(int code, const std::string& m) { g_err = m; return code; }
+#define CU(call)                                                                                        \
+  do {                                                                                                  \
+    cudaError_t e_ = (call);                                                                            \
+    if (e_ != cudaSuccess) return fail(SPT_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+
+struct DevBuf { // one device allocation + the pinned staging copy used by spt_scene_upload
+  void* d = nullptr; void* h = nullptr; size_t bytes = 0;
+};
+
+} // namespace
+
+struct SptContext { int device = 0; int sm_count = 148; };
+
+struct SptScene {
+  SptContext* ctx = nullptr;
+  spt::HostScene hs;
+  DScene ds{};
+  std::vector<DevBuf> bufs;
+  std::vector<DCamera> cameras;
+  // render-time buffers, grown on demand and reused across spt_render calls
+  void* pool_mem = nullptr; size_t pool_bytes = 0; int pool_n = 0;
+  long long* film = nullptr; size_t film_px = 0;
+  DevCounters* ctr = nullptr; uint32_t* sq_count = nullptr;
+  uint32_t* tiles = nullptr; size_t tiles_cap = 0;
+  float* out_mean = nullptr; uint8_t* out_rgb8 = nullptr; size_t out_px = 0;
+  DevCounters* h_ctr = nullptr; // pinned
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+};
+
+namespace {
+
+template <typename T>
+int upload(SptScene* s, const std::vector<T>& v, const T** dptr) {
+  DevBuf b; b.bytes = std::max<size_t>(sizeof(T), v.size() * sizeof(T));
+  CU(cudaMalloc(&b.d, b.bytes));
+  CU(cudaMallocHost(&b.h, b.bytes));
+  memset(b.h, 0, b.bytes);
+  if (!v.empty()) memcpy(b.h, v.data(), v.size() * sizeof(T));
+  CU(cudaMemcpy(b.d, b.h, b.bytes, cudaMemcpyHostToDevice));
+  s->bufs.push_back(b);
+  *dptr = reinterpret_cast<const T*>(b.d);
+  return SPT_OK;
+}
+
+int grid_for(const SptContext* c, long long n, int per_sm) {
+  long long blocks = (n + SPT_BLOCK - 1) / SPT_BLOCK;
+  return (int)std::max<long long>(1, std::min<long long>(blocks, (long long)c->sm_count * per_sm));
+}
+
+__global__ void k_begin_iter(DevCounters* ctr, uint32_t* sq_count) { ctr->live = 0; *sq_count = 0; }
+
+} // namespace
+
+extern "C" {
+
+const char* spt_last_error(void) { return g_err.c_str(); }
+int32_t spt_version(void) { return 100; }
+
+int32_t spt_context_create(int32_t device_id, SptContext** out) {
+  if (!out) return fail(SPT_ERR_INVALID, "spt_context_create: out is null");
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) return fail(SPT_ERR_CUDA, std::string("no CUDA device (this library has no CPU fallback): ") + cudaGetErrorString(e));
+  if (device_id < 0 || device_id >= n) return fail(SPT_ERR_INVALID, "spt_context_create: bad device id");
+  CU(cudaSetDevice(device_id));
+  SptContext* c = new (std::nothrow) SptContext();
+  if (!c) return fail(SPT_ERR_INVALID, "out of host memory");
+  c->device = device_id;
+  cudaDeviceProp p;
+  CU(cudaGetDeviceProperties(&p, device_id));
+  c->sm_count = p.multiProcessorCount;
+  *out = c;
+  return SPT_OK;
+}
+int32_t spt_context_destroy(SptContext* ctx) { delete ctx; return SPT_OK; }
+
+int32_t spt_scene_create(SptContext* ctx, const SptSceneDesc* desc, SptScene** out) {
+  if (!ctx || !desc || !out) return fail(SPT_ERR_INVALID, "spt_scene_create: null argument");
+  CU(cudaSetDevice(ctx->device));
+  SptScene* s = new (std::nothrow) SptScene();
+  if (!s) return fail(SPT_ERR_INVALID, "out of host memory");
+  s->ctx = ctx;
+  const std::string err = spt::flatten_scene(*desc, s->hs);
+  if (!err.empty()) { delete s; return fail(SPT_ERR_INVALID, err); }
+  spt::HostScene& h = s->hs;
+  DScene& d = s->ds;
+  memset(&d, 0, sizeof(d));
+  int st;
+#define UP(vec, field) if ((st = upload(s, vec, &d.field)) != SPT_OK) { spt_scene_destroy(s); return st; }
+  {
+    std::vector<float4> nodes4(h.nodes.size() * 5);
+    if (!h.nodes.empty()) memcpy(nodes4.data(), h.nodes.data(), h.nodes.size() * sizeof(spt::CwNode));
+    UP(nodes4, nodes);
+  }
+  UP(h.tris, tris); UP(h.tlas_inst, tlas_inst); UP(h.inst, inst); UP(h.inst_shade, inst_shade); UP(h.spheres, spheres);
+  UP(h.meshes, meshes); UP(h.verts, verts); UP(h.indices, indices); UP(h.surfaces, surfaces); UP(h.materials, materials);
+  UP(h.textures, textures); UP(h.mips, mips); UP(h.texels, texels); UP(h.mediums, mediums); UP(h.lights, lights);
+  UP(h.light_prob, light_prob); UP(h.light_alias, light_alias); UP(h.inst_light, inst_light); UP(h.ss_cdf, ss_cdf);
+  if (h.env_w > 0) { UP(h.env_tex, env_tex); UP(h.env_alias, env_alias); }
+#undef UP
+  for (int c = 0; c < 3; c++) d.env_scale[c] = h.env_scale[c];
+  d.env_w = h.env_w; d.env_h = h.env_h;
+  d.n_lights = (int32_t)h.lights.size(); d.light_sampler = h.light_sampler; d.env_light_index = h.env_light_index;
+  d.n_instances = (int32_t)h.inst.size(); d.tlas_empty = h.nodes.empty() || h.inst.empty();
+  d.has_image_tex = h.has_image_tex ? 1 : 0;
+  d.num_light_inv = 1.0f / (float)h.lights.size(); // UniformLightSampler::new, uniform.rs:19
+  s->cameras = h.cameras;
+  d.camera = s->cameras[0];
+  CU(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+  CU(cudaEventCreate(&s->ev[0])); CU(cudaEventCreate(&s->ev[1]));
+  CU(cudaMalloc(&s->ctr, sizeof(DevCounters))); CU(cudaMalloc(&s->sq_count, sizeof(uint32_t)));
+  CU(cudaMallocHost(&s->h_ctr, sizeof(DevCounters)));
+  *out = s;
+  return SPT_OK;
+}
+
+int32_t spt_scene_upload(SptScene* s, int64_t* bytes_copied) {
+  if (!s) return fail(SPT_ERR_INVALID, "spt_scene_upload: null scene");
+  CU(cudaSetDevice(s->ctx->device));
+  int64_t total = 0;
+  for (const DevBuf& b : s->bufs) { CU(cudaMemcpyAsync(b.d, b.h, b.bytes, cudaMemcpyHostToDevice, s->stream)); total += (int64_t)b.bytes; }
+  CU(cudaStreamSynchronize(s->stream));
+  if (bytes_copied) *bytes_copied = total;
+  return SPT_OK;
+}
+
+int32_t spt_scene_info(const SptScene* s, SptSceneInfo* out) {
+  if (!s || !out) return fail(SPT_ERR_INVALID, "spt_scene_info: null argument");
+  out->tlas_nodes = s->hs.tlas_nodes; out->blas_nodes = s->hs.blas_nodes;
+  out->triangles = (int64_t)(s->hs.tris.size() / 3); out->instances = (int64_t)s->hs.inst.size();
+  out->bytes_nodes = (int64_t)(s->hs.nodes.size() * sizeof(spt::CwNode)); out->bytes_tris = (int64_t)(s->hs.tris.size() * sizeof(float4));
+  int64_t t = 0; for (const DevBuf& b : s->bufs) t += (int64_t)b.bytes;
+  out->bytes_total = t;
+  return SPT_OK;
+}
+
+int32_t spt_scene_destroy(SptScene* s) {
+  if (!s) return SPT_OK;
+  cudaSetDevice(s->ctx->device);
+  for (DevBuf& b : s->bufs) { cudaFree(b.d); cudaFreeHost(b.h); }
+  cudaFree(s->pool_mem); cudaFree(s->film); cudaFree(s->ctr); cudaFree(s->sq_count); cudaFree(s->tiles);
+  cudaFree(s->out_mean); cudaFree(s->out_rgb8); cudaFreeHost(s->h_ctr);
+  if (s->ev[0]) cudaEventDestroy(s->ev[0]);
+  if (s->ev[1]) cudaEventDestroy(s->ev[1]);
+  if (s->stream) cudaStreamDestroy(s->stream);
+  delete s;
+  return SPT_OK;
+}
+
+// ---- seam B2 ---------------------------------------------------------------------------------------------------
+static int32_t batch_device(SptScene* s, const SptRay* d_rays, int64_t n, void* d_out, bool any, uint32_t flags, SptStats* stats, void* stream_) {
+  if (!s || (n > 0 && (!d_rays || !d_out)) || n < 0) return fail(SPT_ERR_INVALID, "ray batch: bad argument");
+  CU(cudaSetDevice(s->ctx->device));
+  cudaStream_t st = stream_ ? (cudaStream_t)stream_ : s->stream;
+  const bool count = (flags & SPT_RENDER_COUNT_TRAVERSAL) != 0;
+  if (count) CU(cudaMemsetAsync(s->ctr, 0, sizeof(DevCounters), st));
+  if (n > 0) {
+    const int grid = grid_for(s->ctx, n, 16);
+    const float4* r4 = reinterpret_cast<const float4*>(d_rays);
+    if (!any) { if (count) k_trace_batch<true><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4, n, (HitIO*)d_out, s->ctr); else k_trace_batch<false><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4, n, (HitIO*)d_out, nullptr); }
+    else { if (count) k_occluded_batch<true><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4, n, (uint8_t*)d_out, s->ctr); else k_occluded_batch<false><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4, n, (uint8_t*)d_out, nullptr); }
+    CU(cudaGetLastError());
+  }
+  if (stats) {
+    memset(stats, 0, sizeof(*stats));
+    if (any) stats->shadow_rays = (uint64_t)n; else stats->ext_rays = (uint64_t)n;
+    stats->kernel_launches = n > 0 ? 1 : 0;
+    if (count) {
+      CU(cudaMemcpyAsync(s->h_ctr, s->ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      stats->nodes_visited = s->h_ctr->nodes; stats->tris_tested = s->h_ctr->tris; stats->insts_visited = s->h_ctr->insts;
+    }
+  }
+  return SPT_OK;
+}
+int32_t spt_trace_batch_device(SptScene* s, const SptRay* d_rays, int64_t n, SptHit* d_hits, uint32_t flags, SptStats* stats, void* stream) {
+  return batch_device(s, d_rays, n, d_hits, false, flags, stats, stream);
+}
+int32_t spt_occluded_batch_device(SptScene* s, const SptRay* d_rays, int64_t n, uint8_t* d_out, uint32_t flags, SptStats* stats, void* stream) {
+  return batch_device(s, d_rays, n, d_out, true, flags, stats, stream);
+}
+static int32_t batch_host(SptScene* s, const SptRay* rays, int64_t n, void* out, size_t out_elem, bool any) {
+  if (!s || (n > 0 && (!rays || !out)) || n < 0) return fail(SPT_ERR_INVALID, "ray batch: bad argument");
+  if (n == 0) return SPT_OK;
+  CU(cudaSetDevice(s->ctx->device));
+  SptRay* d_r = nullptr; void* d_o = nullptr;
+  CU(cudaMalloc(&d_r, (size_t)n * sizeof(SptRay)));
+  if (cudaMalloc(&d_o, (size_t)n * out_elem) != cudaSuccess) { cudaFree(d_r); return fail(SPT_ERR_CUDA, "cudaMalloc failed"); }
+  int32_t st = SPT_OK;
+  if (cudaMemcpyAsync(d_r, rays, (size_t)n * sizeof(SptRay), cudaMemcpyHostToDevice, s->stream) != cudaSuccess) st = fail(SPT_ERR_CUDA, "H2D failed");
+  if (st == SPT_OK) st = batch_device(s, d_r, n, d_o, any, 0, nullptr, nullptr);
+  if (st == SPT_OK && cudaMemcpyAsync(out, d_o, (size_t)n * out_elem, cudaMemcpyDeviceToHost, s->stream) != cudaSuccess) st = fail(SPT_ERR_CUDA, "D2H failed");
+  if (st == SPT_OK) { cudaError_t e = cudaStreamSynchronize(s->stream); if (e != cudaSuccess) st = fail(SPT_ERR_CUDA, std::string("ray batch: ") + cudaGetErrorString(e)); }
+  cudaFree(d_r); cudaFree(d_o);
+  return st;
+}
+int32_t spt_trace_batch(SptScene* s, const SptRay* rays, int64_t n, SptHit* out) { return batch_host(s, rays, n, out, sizeof(SptHit), false); }
+int32_t spt_occluded_batch(SptScene* s, const SptRay* rays, int64_t n, uint8_t* out) { return batch_host(s, rays, n, out, 1, true); }
+
+} // extern "C"
+
+// ---- BxDF test hook -----------------------------------------------------------------------------------------------
+namespace {
+__global__ void k_bxdf_batch(const DScene sc, const SptBxdfQuery* __restrict__ q, long long n, SptBxdfResult* __restrict__ out) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const SptBxdfQuery Q = q[i];
+    HitGeom g; g.p = mk3(0.f); g.n = mk3(0, 0, 1); g.tan = mk3(1, 0, 0); g.bitan = mk3(0, 1, 0);
+    g.uv = make_float2(Q.texcoord[0], Q.texcoord[1]); g.duvdx = g.duvdy = make_float2(0.f, 0.f);
+    const Bsdf b = make_bsdf(sc, sc.materials[Q.material], texin_from(g));
+    DrawSrc rng; rng.state = 0; rng.list = q[i].rand; rng.idx = 0; rng.n = 8;
+    const float3 wo = mk3(Q.wo[0], Q.wo[1], Q.wo[2]), wi = mk3(Q.wi[0], Q.wi[1], Q.wi[2]);
+    BsdfSample s;
+    bsdf_sample(b, wo, rng, s);
+    SptBxdfResult R;
+    if (s.need_probe) { rng.next(); rng.next(); rng.next(); s.lobe = -1; } // no scene in the hook: probe cannot run
+    R.sample_wi[0] = s.wi.x; R.sample_wi[1] = s.wi.y; R.sample_wi[2] = s.wi.z;
+    R.sample_f[0] = s.f.x; R.sample_f[1] = s.f.y; R.sample_f[2] = s.f.z;
+    R.sample_pdf = s.pdf; R.sample_lobe = s.lobe; R.sample_dir = s.dir; R.n_rand_used = rng.idx;
+    const float3 f = bsdf_eval(b, wo, wi);
+    R.eval_f[0] = f.x; R.eval_f[1] = f.y; R.eval_f[2] = f.z; R.eval_pdf = bsdf_pdf(b, wo, wi);
+    R.is_delta = bsdf_is_delta(b) ? 1 : 0; R.bxdf_tag = b.tag;
+    out[i] = R;
+  }
+}
+} // namespace
+
+extern "C" int32_t spt_bxdf_batch(SptScene* s, const SptBxdfQuery* queries, int64_t n, SptBxdfResult* out) {
+  if (!s || n < 0 || (n > 0 && (!queries || !out))) return fail(SPT_ERR_INVALID, "spt_bxdf_batch: bad argument");
+  if (n == 0) return SPT_OK;
+  for (int64_t i = 0; i < n; i++) if (queries[i].material < 0 || queries[i].material >= (int)s->hs.materials.size()) return fail(SPT_ERR_INVALID, "spt_bxdf_batch: bad material index");
+  CU(cudaSetDevice(s->ctx->device));
+  SptBxdfQuery* dq = nullptr; SptBxdfResult* dr = nullptr;
+  CU(cudaMalloc(&dq, (size_t)n * sizeof(SptBxdfQuery)));
+  if (cudaMalloc(&dr, (size_t)n * sizeof(SptBxdfResult)) != cudaSuccess) { cudaFree(dq); return fail(SPT_ERR_CUDA, "cudaMalloc failed"); }
+  cudaMemcpyAsync(dq, queries, (size_t)n * sizeof(SptBxdfQuery), cudaMemcpyHostToDevice, s->stream);
+  k_bxdf_batch<<<grid_for(s->ctx, n, 8), SPT_BLOCK, 0, s->stream>>>(s->ds, dq, n, dr);
+  cudaMemcpyAsync(out, dr, (size_t)n * sizeof(SptBxdfResult), cudaMemcpyDeviceToHost, s->stream);
+  cudaError_t e = cudaStreamSynchronize(s->stream);
+  cudaFree(dq); cudaFree(dr);
+  if (e != cudaSuccess) return fail(SPT_ERR_CUDA, std::string("spt_bxdf_batch: ") + cudaGetErrorString(e));
+  return SPT_OK;
+}
+
+// ---- seam B1: RendererT::render ------------------------------------------------------------------------------------------
+namespace {
+
+uint32_t tile_hash(uint32_t t) { t ^= t >> 16; t *= 0x7feb352du; t ^= t >> 15; t *= 0x846ca68bu; t ^= t >> 16; return t; }
+
+int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_rgb8, SptStats* stats) {
+  if (!s || !r || !d_mean) return fail(SPT_ERR_INVALID, "spt_render: null argument");
+  if (r->width <= 0 || r->height <= 0 || r->max_depth < 0 || r->max_depth > 255) return fail(SPT_ERR_INVALID, "spt_render: bad width/height/max_depth");
+  if (r->camera_index < 0 || r->camera_index >= (int)s->cameras.size()) return fail(SPT_ERR_INVALID, "spt_render: bad camera index");
+  if (r->sampler_kind < 0 || r->sampler_kind > 2) return fail(SPT_ERR_INVALID, "spt_render: unknown sampler");
+  if (r->filter_radius > 0.5f) return fail(SPT_ERR_UNSUPPORTED, "spt_render: only the box filter with radius <= 0.5 (own-pixel mean) is supported");
+  if (s->hs.lights.empty()) return fail(SPT_ERR_UNSUPPORTED, "spt_render: the scene has no light (the reference's light sampler would panic)");
+  const int world = std::max(1, r->world_size), rank = r->rank;
+  if (rank < 0 || rank >= world) return fail(SPT_ERR_INVALID, "spt_render: bad rank");
+  const int spp = r->sampler_kind == SPT_SAMPLER_JITTERED ? std::max(1, r->div_x) * std::max(1, r->div_y) : std::max(1, r->spp);
+  const int tw = r->tile_w > 0 ? r->tile_w : 32, th = r->tile_h > 0 ? r->tile_h : 32;
+  if (tw % 8 || th % 4) return fail(SPT_ERR_INVALID, "spt_render: tile_w must be a multiple of 8 and tile_h of 4");
+  CU(cudaSetDevice(s->ctx->device));
+  cudaStream_t st = s->stream;
+  const size_t n_px = (size_t)r->width * r->height;
+  // ---- buffers
+  int pool_n = r->pool_size > 0 ? r->pool_size : (1 << 20);
+  pool_n = std::max(SPT_BLOCK, (pool_n + SPT_BLOCK - 1) / SPT_BLOCK * SPT_BLOCK);
+  const size_t per_slot = 4 * sizeof(float4) + sizeof(int32_t) + sizeof(uint64_t) + 3 * sizeof(uint32_t) + 3 * sizeof(float4);
+  if (s->pool_n != pool_n) {
+    cudaFree(s->pool_mem); s->pool_mem = nullptr; s->pool_n = 0;
+    CU(cudaMalloc(&s->pool_mem, per_slot * (size_t)pool_n));
+    s->pool_n = pool_n; s->pool_bytes = per_slot * (size_t)pool_n;
+  }
+  if (s->film_px < n_px) { cudaFree(s->film); s->film = nullptr; CU(cudaMalloc(&s->film, n_px * 3 * sizeof(long long))); s->film_px = n_px; }
+  RenderParams P; memset(&P, 0, sizeof(P));
+  {
+    char* p = (char*)s->pool_mem; const size_t N = (size_t)pool_n;
+    P.pool.ray_o = (float4*)p; p += N * sizeof(float4);
+    P.pool.ray_d = (float4*)p; p += N * sizeof(float4);
+    P.pool.hit = (float4*)p; p += N * sizeof(float4);
+    P.pool.thr = (float4*)p; p += N * sizeof(float4);
+    P.sq.o = (float4*)p; p += N * sizeof(float4);
+    P.sq.d = (float4*)p; p += N * sizeof(float4);
+    P.sq.c = (float4*)p; p += N * sizeof(float4);
+    P.pool.rng = (uint64_t*)p; p += N * sizeof(uint64_t);
+    P.pool.hit_inst = (int32_t*)p; p += N * sizeof(int32_t);
+    P.pool.pixel = (uint32_t*)p; p += N * sizeof(uint32_t);
+    P.pool.sample = (uint32_t*)p; p += N * sizeof(uint32_t);
+    P.pool.flags = (uint32_t*)p; p += N * sizeof(uint32_t);
+    P.pool.n = pool_n;
+  }
+  P.sq.count = s->sq_count; P.ctr = s->ctr; P.film = s->film;
+  // ---- tile ownership: tiles sorted by a hash, dealt round-robin -> interleaved, balanced to +-1 tile
+  const int tiles_x = (r->width + tw - 1) / tw, tiles_y = (r->height + th - 1) / th, n_all = tiles_x * tiles_y;
+  std::vector<std::pair<uint32_t, uint32_t>> order(n_all);
+  for (int t = 0; t < n_all; t++) order[t] = {tile_hash((uint32_t)t), (uint32_t)t};
+  if (world > 1) std::sort(order.begin(), order.end());
+  std::vector<uint32_t> mine;
+  for (int i = rank; i < n_all; i += world) mine.push_back(order[i].second);
+  std::sort(mine.begin(), mine.end());
+  if (s->tiles_cap < mine.size()) { cudaFree(s->tiles); s->tiles = nullptr; CU(cudaMalloc(&s->tiles, std::max<size_t>(1, mine.size()) * sizeof(uint32_t))); s->tiles_cap = mine.size(); }
+  if (!mine.empty()) CU(cudaMemcpyAsync(s->tiles, mine.data(), mine.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+  P.tiles = s->tiles; P.n_tiles = (int)mine.size(); P.tiles_x = tiles_x; P.tile_w = tw; P.tile_h = th;
+  P.width = r->width; P.height = r->height; P.max_depth = r->max_depth;
+  P.sampler = r->sampler_kind; P.spp = spp; P.div_x = std::max(1, r->div_x); P.div_y = std::max(1, r->div_y);
+  P.seed = r->seed;
+  P.total_samples = (unsigned long long)mine.size() * (unsigned long long)(tw * th) * (unsigned long long)spp;
+  DScene ds = s->ds;
+  ds.camera = s->cameras[r->camera_index];
+  const bool count = (r->flags & SPT_RENDER_COUNT_TRAVERSAL) != 0;
+  // ---- run
+  CU(cudaMemsetAsync(s->film, 0, n_px * 3 * sizeof(long long), st));
+  CU(cudaMemsetAsync(s->ctr, 0, sizeof(DevCounters), st));
+  CU(cudaMemsetAsync(P.pool.flags, 0, (size_t)pool_n * sizeof(uint32_t), st));
+  CU(cudaEventRecord(s->ev[0], st));
+  const int grid = grid_for(s->ctx, pool_n, 16);
+  uint64_t iters = 0, launches = 0;
+  if (r->max_depth > 0 && P.total_samples > 0) {
+    for (;;) {
+      k_begin_iter<<<1, 1, 0, st>>>(s->ctr, s->sq_count);
+      if (count) { k_shade<true><<<grid, SPT_BLOCK, 0, st>>>(ds, P); k_connect<true><<<grid, SPT_BLOCK, 0, st>>>(ds, P); k_extend<true><<<grid, SPT_BLOCK, 0, st>>>(ds, P); }
+      else { k_shade<false><<<grid, SPT_BLOCK, 0, st>>>(ds, P); k_connect<false><<<grid, SPT_BLOCK, 0, st>>>(ds, P); k_extend<false><<<grid, SPT_BLOCK, 0, st>>>(ds, P); }
+      launches += 4; iters++;
+      CU(cudaMemcpyAsync(s->h_ctr, s->ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      CU(cudaGetLastError());
+      if (s->h_ctr->live == 0) break;
+    }
+  }
+  k_resolve<<<grid_for(s->ctx, (long long)n_px * 3, 8), 256, 0, st>>>(s->film, (int)n_px, 1.0f / (float)spp, d_mean, d_rgb8);
+  launches++;
+  CU(cudaEventRecord(s->ev[1], st));
+  CU(cudaMemcpyAsync(s->h_ctr, s->ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  CU(cudaGetLastError());
+  if (stats) {
+    memset(stats, 0, sizeof(*stats));
+    float ms = 0.f; cudaEventElapsedTime(&ms, s->ev[0], s->ev[1]);
+    const DevCounters& c = *s->h_ctr;
+    stats->paths = c.paths; stats->ext_rays = c.ext_rays; stats->shadow_rays = c.shadow_rays; stats->probe_rays = c.probe_rays;
+    stats->nodes_visited = c.nodes; stats->tris_tested = c.tris; stats->insts_visited = c.insts; stats->nonfinite = c.nonfinite;
+    stats->iterations = iters; stats->kernel_launches = launches; stats->seconds_total = ms * 1e-3;
+  }
+  return SPT_OK;
+}
+
+} // namespace
+
+extern "C" int32_t spt_render_device(SptScene* s, const SptRenderDesc* r, float* d_rgb_mean, SptStats* stats) {
+  return render_impl(s, r, d_rgb_mean, nullptr, stats);
+}
+
+extern "C" int32_t spt_render(SptScene* s, const SptRenderDesc* r, float* out_rgb_mean, uint8_t* out_rgb8, SptStats* stats) {
+  if (!s || !r || !out_rgb_mean) return fail(SPT_ERR_INVALID, "spt_render: null argument");
+  if (r->width <= 0 || r->height <= 0) return fail(SPT_ERR_INVALID, "spt_render: bad width/height");
+  CU(cudaSetDevice(s->ctx->device));
+  const size_t n_px = (size_t)r->width * r->height;
+  if (s->out_px < n_px) {
+    cudaFree(s->out_mean); cudaFree(s->out_rgb8); s->out_mean = nullptr; s->out_rgb8 = nullptr; s->out_px = 0;
+    CU(cudaMalloc(&s->out_mean, n_px * 3 * sizeof(float))); CU(cudaMalloc(&s->out_rgb8, n_px * 3));
+    s->out_px = n_px;
+  }
+  const int st = render_impl(s, r, s->out_mean, out_rgb8 ? s->out_rgb8 : nullptr, stats);
+  if (st != SPT_OK) return st;
+  CU(cudaMemcpyAsync(out_rgb_mean, s->out_mean, n_px * 3 * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+  if (out_rgb8) CU(cudaMemcpyAsync(out_rgb8, s->out_rgb8, n_px * 3, cudaMemcpyDeviceToHost, s->stream));
+  CU(cudaStreamSynchronize(s->stream));
+  return SPT_OK;
+}

@@ -1,0 +1,109 @@
+"""Thin Python handles over the C ABI (include/spt.h): Context, Scene (device-resident flattened scene) and the
+calls a host makes on them.  All compute happens in libspt_cuda.so; nothing here falls back to the CPU."""
+import ctypes as C
+
+import numpy as np
+
+from . import abi
+
+RAY_DT = np.dtype([("origin", "<f4", 3), ("t_min", "<f4"), ("direction", "<f4", 3), ("t_max", "<f4")])
+HIT_DT = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim_id", "<i4"), ("inst_id", "<i4")])
+
+
+class Context:
+    def __init__(self, device=0):
+        self.lib = abi.load_library()
+        self.h = C.c_void_p()
+        abi.check(self.lib, self.lib.spt_context_create(device, C.byref(self.h)))
+        self.device = device
+
+    def close(self):
+        if self.h:
+            self.lib.spt_context_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+class Scene:
+    """spt_scene_create on a FlatScene (spt.loader)."""
+
+    def __init__(self, ctx, flat_scene):
+        self.ctx, self.lib, self.fs = ctx, ctx.lib, flat_scene
+        desc = flat_scene.to_desc()
+        self.h = C.c_void_p()
+        abi.check(self.lib, self.lib.spt_scene_create(ctx.h, C.byref(desc), C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            self.lib.spt_scene_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self):
+        i = abi.SceneInfo()
+        abi.check(self.lib, self.lib.spt_scene_info(self.h, C.byref(i)))
+        return {k: getattr(i, k) for k, _ in i._fields_}
+
+    def upload(self):
+        n = C.c_int64()
+        abi.check(self.lib, self.lib.spt_scene_upload(self.h, C.byref(n)))
+        return n.value
+
+    # ---- seam B2
+    def trace(self, rays):
+        rays = np.ascontiguousarray(rays, RAY_DT)
+        hits = np.zeros(len(rays), HIT_DT)
+        abi.check(self.lib, self.lib.spt_trace_batch(self.h, rays.ctypes.data, len(rays), hits.ctypes.data))
+        return hits
+
+    def occluded(self, rays):
+        rays = np.ascontiguousarray(rays, RAY_DT)
+        out = np.zeros(len(rays), np.uint8)
+        abi.check(self.lib, self.lib.spt_occluded_batch(self.h, rays.ctypes.data, len(rays), out.ctypes.data))
+        return out
+
+    def trace_device(self, d_rays_ptr, n, d_hits_ptr, flags=0, stream=None, want_stats=False):
+        st = abi.Stats()
+        abi.check(self.lib, self.lib.spt_trace_batch_device(self.h, d_rays_ptr, n, d_hits_ptr, flags,
+                                                            C.byref(st) if want_stats else None, stream))
+        return st.as_dict() if want_stats else None
+
+    def occluded_device(self, d_rays_ptr, n, d_out_ptr, flags=0, stream=None, want_stats=False):
+        st = abi.Stats()
+        abi.check(self.lib, self.lib.spt_occluded_batch_device(self.h, d_rays_ptr, n, d_out_ptr, flags,
+                                                               C.byref(st) if want_stats else None, stream))
+        return st.as_dict() if want_stats else None
+
+    def bxdf(self, queries):
+        n = len(queries)
+        q = (abi.BxdfQuery * n)(*queries)
+        r = (abi.BxdfResult * n)()
+        abi.check(self.lib, self.lib.spt_bxdf_batch(self.h, q, n, r))
+        return list(r)
+
+    # ---- seam B1
+    def render_desc(self, width, height, spp=16, max_depth=8, sampler="recurrence", div=(1, 1), seed=1, camera=0,
+                    rank=0, world_size=1, pool_size=0, flags=0, tile=(0, 0), filter_radius=0.5):
+        return abi.RenderDesc(camera, width, height, max_depth, abi.SAMPLER[sampler], spp, div[0], div[1], filter_radius,
+                              seed, tile[0], tile[1], rank, world_size, pool_size, flags)
+
+    def render(self, width, height, want_rgb8=False, **kw):
+        """spt_render: host buffers out.  Returns (mean image [H,W,3] f32, stats) or (mean, rgb8, stats)."""
+        rd = self.render_desc(width, height, **kw)
+        img = np.zeros((height, width, 3), np.float32)
+        rgb8 = np.zeros((height, width, 3), np.uint8) if want_rgb8 else None
+        st = abi.Stats()
+        abi.check(self.lib, self.lib.spt_render(self.h, C.byref(rd), img.ctypes.data,
+                                                rgb8.ctypes.data if want_rgb8 else None, C.byref(st)))
+        return (img, rgb8, st.as_dict()) if want_rgb8 else (img, st.as_dict())
+
+    def render_device(self, d_out_ptr, width, height, **kw):
+        """spt_render_device: result stays in device memory at d_out_ptr (width*height*3 f32)."""
+        rd = self.render_desc(width, height, **kw)
+        st = abi.Stats()
+        abi.check(self.lib, self.lib.spt_render_device(self.h, C.byref(rd), d_out_ptr, C.byref(st)))
+        return st.as_dict()
