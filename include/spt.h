@@ -220,6 +220,7 @@ typedef struct SptBxdfResult {
 
 #define SPT_RENDER_COUNT_TRAVERSAL 1u /* fill nodes_visited/tris_tested/insts_visited (slower build) */
 #define SPT_RENDER_NO_SORT 2u         /* disable material binning of the shade stage (for A/B timing) */
+#define SPT_RENDER_TIME_STAGES 4u     /* fill seconds_stage[] from CUDA events around every kernel launch */
 
 typedef struct SptRenderDesc { /* OutputConfig (renderer/mod.rs:9-14) + PathTracer fields (pt.rs:24-28) */
   int32_t camera_index;
@@ -294,6 +295,13 @@ int32_t spt_render(SptScene* scene, const SptRenderDesc* desc, float* out_rgb_me
 /* Same, result left in device memory (width*height*3 f32; pixels of other ranks are 0) so the
  * host can reduce it over NCCL without a round trip. */
 int32_t spt_render_device(SptScene* scene, const SptRenderDesc* desc, float* d_rgb_mean, SptStats* stats);
+
+/* Host-only helper (no device needed): the ids of the screen tiles rank `rank` of `world_size` owns for a
+ * width x height image cut into tile_w x tile_h tiles (0 = 32).  Tiles are dealt round-robin in hash order, so
+ * every rank gets a spatially interleaved share balanced to +-1 tile (replaces the contiguous row bands of
+ * renderer/util.rs:6-19).  Writes at most `cap` ids (row-major tile index) and returns the count in *n_out. */
+int32_t spt_owned_tiles(int32_t width, int32_t height, int32_t tile_w, int32_t tile_h, int32_t rank, int32_t world_size,
+                        uint32_t* out, int64_t cap, int64_t* n_out);
 
 #ifdef __cplusplus
 }

@@ -42,6 +42,7 @@ struct SptScene {
   DevCounters* h_ctr = nullptr; // pinned
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[2] = {nullptr, nullptr};
+  cudaEvent_t sev[4] = {nullptr, nullptr, nullptr, nullptr}; // per-stage timing (SPT_RENDER_TIME_STAGES)
 };
 
 namespace {
@@ -125,6 +126,7 @@ int32_t spt_scene_create(SptContext* ctx, const SptSceneDesc* desc, SptScene** o
   d.camera = s->cameras[0];
   CU(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
   CU(cudaEventCreate(&s->ev[0])); CU(cudaEventCreate(&s->ev[1]));
+  for (int i = 0; i < 4; i++) CU(cudaEventCreate(&s->sev[i]));
   CU(cudaMalloc(&s->ctr, sizeof(DevCounters))); CU(cudaMalloc(&s->sq_count, sizeof(uint32_t)));
   CU(cudaMallocHost(&s->h_ctr, sizeof(DevCounters)));
   *out = s;
@@ -159,6 +161,7 @@ int32_t spt_scene_destroy(SptScene* s) {
   cudaFree(s->out_mean); cudaFree(s->out_rgb8); cudaFreeHost(s->h_ctr);
   if (s->ev[0]) cudaEventDestroy(s->ev[0]);
   if (s->ev[1]) cudaEventDestroy(s->ev[1]);
+  for (int i = 0; i < 4; i++) if (s->sev[i]) cudaEventDestroy(s->sev[i]);
   if (s->stream) cudaStreamDestroy(s->stream);
   delete s;
   return SPT_OK;
@@ -263,6 +266,17 @@ namespace {
 
 uint32_t tile_hash(uint32_t t) { t ^= t >> 16; t *= 0x7feb352du; t ^= t >> 15; t *= 0x846ca68bu; t ^= t >> 16; return t; }
 
+std::vector<uint32_t> owned_tiles(int width, int height, int tw, int th, int rank, int world) {
+  const int tiles_x = (width + tw - 1) / tw, tiles_y = (height + th - 1) / th, n_all = tiles_x * tiles_y;
+  std::vector<std::pair<uint32_t, uint32_t>> order(n_all);
+  for (int t = 0; t < n_all; t++) order[t] = {tile_hash((uint32_t)t), (uint32_t)t};
+  if (world > 1) std::sort(order.begin(), order.end());
+  std::vector<uint32_t> mine;
+  for (int i = rank; i < n_all; i += world) mine.push_back(order[i].second);
+  std::sort(mine.begin(), mine.end());
+  return mine;
+}
+
 int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_rgb8, SptStats* stats) {
   if (!s || !r || !d_mean) return fail(SPT_ERR_INVALID, "spt_render: null argument");
   if (r->width <= 0 || r->height <= 0 || r->max_depth < 0 || r->max_depth > 255) return fail(SPT_ERR_INVALID, "spt_render: bad width/height/max_depth");
@@ -307,13 +321,8 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   }
   P.sq.count = s->sq_count; P.ctr = s->ctr; P.film = s->film;
   // ---- tile ownership: tiles sorted by a hash, dealt round-robin -> interleaved, balanced to +-1 tile
-  const int tiles_x = (r->width + tw - 1) / tw, tiles_y = (r->height + th - 1) / th, n_all = tiles_x * tiles_y;
-  std::vector<std::pair<uint32_t, uint32_t>> order(n_all);
-  for (int t = 0; t < n_all; t++) order[t] = {tile_hash((uint32_t)t), (uint32_t)t};
-  if (world > 1) std::sort(order.begin(), order.end());
-  std::vector<uint32_t> mine;
-  for (int i = rank; i < n_all; i += world) mine.push_back(order[i].second);
-  std::sort(mine.begin(), mine.end());
+  const int tiles_x = (r->width + tw - 1) / tw;
+  const std::vector<uint32_t> mine = owned_tiles(r->width, r->height, tw, th, rank, world);
   if (s->tiles_cap < mine.size()) { cudaFree(s->tiles); s->tiles = nullptr; CU(cudaMalloc(&s->tiles, std::max<size_t>(1, mine.size()) * sizeof(uint32_t))); s->tiles_cap = mine.size(); }
   if (!mine.empty()) CU(cudaMemcpyAsync(s->tiles, mine.data(), mine.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
   P.tiles = s->tiles; P.n_tiles = (int)mine.size(); P.tiles_x = tiles_x; P.tile_w = tw; P.tile_h = th;
@@ -331,15 +340,27 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   CU(cudaEventRecord(s->ev[0], st));
   const int grid = grid_for(s->ctx, pool_n, 16);
   uint64_t iters = 0, launches = 0;
+  const bool timed = (r->flags & SPT_RENDER_TIME_STAGES) != 0;
+  double stage[6] = {0, 0, 0, 0, 0, 0}; // generate (fused into shade), extend, shade, connect, resolve, other
   if (r->max_depth > 0 && P.total_samples > 0) {
     for (;;) {
       k_begin_iter<<<1, 1, 0, st>>>(s->ctr, s->sq_count);
-      if (count) { k_shade<true><<<grid, SPT_BLOCK, 0, st>>>(ds, P); k_connect<true><<<grid, SPT_BLOCK, 0, st>>>(ds, P); k_extend<true><<<grid, SPT_BLOCK, 0, st>>>(ds, P); }
-      else { k_shade<false><<<grid, SPT_BLOCK, 0, st>>>(ds, P); k_connect<false><<<grid, SPT_BLOCK, 0, st>>>(ds, P); k_extend<false><<<grid, SPT_BLOCK, 0, st>>>(ds, P); }
+      if (timed) cudaEventRecord(s->sev[0], st);
+      if (count) k_shade<true><<<grid, SPT_BLOCK, 0, st>>>(ds, P); else k_shade<false><<<grid, SPT_BLOCK, 0, st>>>(ds, P);
+      if (timed) cudaEventRecord(s->sev[1], st);
+      if (count) k_connect<true><<<grid, SPT_BLOCK, 0, st>>>(ds, P); else k_connect<false><<<grid, SPT_BLOCK, 0, st>>>(ds, P);
+      if (timed) cudaEventRecord(s->sev[2], st);
+      if (count) k_extend<true><<<grid, SPT_BLOCK, 0, st>>>(ds, P); else k_extend<false><<<grid, SPT_BLOCK, 0, st>>>(ds, P);
+      if (timed) cudaEventRecord(s->sev[3], st);
       launches += 4; iters++;
       CU(cudaMemcpyAsync(s->h_ctr, s->ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, st));
       CU(cudaStreamSynchronize(st));
       CU(cudaGetLastError());
+      if (timed) {
+        float a = 0, b = 0, c = 0;
+        cudaEventElapsedTime(&a, s->sev[0], s->sev[1]); cudaEventElapsedTime(&b, s->sev[1], s->sev[2]); cudaEventElapsedTime(&c, s->sev[2], s->sev[3]);
+        stage[2] += a * 1e-3; stage[3] += b * 1e-3; stage[1] += c * 1e-3;
+      }
       if (s->h_ctr->live == 0) break;
     }
   }
@@ -356,6 +377,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
     stats->paths = c.paths; stats->ext_rays = c.ext_rays; stats->shadow_rays = c.shadow_rays; stats->probe_rays = c.probe_rays;
     stats->nodes_visited = c.nodes; stats->tris_tested = c.tris; stats->insts_visited = c.insts; stats->nonfinite = c.nonfinite;
     stats->iterations = iters; stats->kernel_launches = launches; stats->seconds_total = ms * 1e-3;
+    for (int i = 0; i < 6; i++) stats->seconds_stage[i] = stage[i];
   }
   return SPT_OK;
 }
@@ -381,5 +403,15 @@ extern "C" int32_t spt_render(SptScene* s, const SptRenderDesc* r, float* out_rg
   CU(cudaMemcpyAsync(out_rgb_mean, s->out_mean, n_px * 3 * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
   if (out_rgb8) CU(cudaMemcpyAsync(out_rgb8, s->out_rgb8, n_px * 3, cudaMemcpyDeviceToHost, s->stream));
   CU(cudaStreamSynchronize(s->stream));
+  return SPT_OK;
+}
+
+extern "C" int32_t spt_owned_tiles(int32_t width, int32_t height, int32_t tile_w, int32_t tile_h, int32_t rank, int32_t world_size,
+                                   uint32_t* out, int64_t cap, int64_t* n_out) {
+  const int tw = tile_w > 0 ? tile_w : 32, th = tile_h > 0 ? tile_h : 32;
+  if (width <= 0 || height <= 0 || world_size <= 0 || rank < 0 || rank >= world_size || !n_out) return fail(SPT_ERR_INVALID, "spt_owned_tiles: bad argument");
+  const std::vector<uint32_t> mine = owned_tiles(width, height, tw, th, rank, world_size);
+  *n_out = (int64_t)mine.size();
+  for (int64_t i = 0; i < (int64_t)mine.size() && i < cap && out; i++) out[i] = mine[i];
   return SPT_OK;
 }

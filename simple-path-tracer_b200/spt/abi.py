@@ -22,6 +22,7 @@ SAMPLER = dict(random=0, jittered=1, recurrence=2)
 AGG = dict(group=0, bvh=1)
 RENDER_COUNT_TRAVERSAL = 1
 RENDER_NO_SORT = 2
+RENDER_TIME_STAGES = 4
 
 
 class MeshDesc(C.Structure):
@@ -131,7 +132,7 @@ class SceneInfo(C.Structure):
 SYMBOLS = ["spt_last_error", "spt_version", "spt_context_create", "spt_context_destroy", "spt_scene_create",
            "spt_scene_upload", "spt_scene_info", "spt_scene_destroy", "spt_trace_batch", "spt_occluded_batch",
            "spt_trace_batch_device", "spt_occluded_batch_device", "spt_bxdf_batch", "spt_render",
-           "spt_render_device"]
+           "spt_render_device", "spt_owned_tiles"]
 
 PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_PATH = os.path.join(PKG_ROOT, "lib", "libspt_cuda.so")
@@ -169,6 +170,7 @@ def load_library(path=None):
         "spt_bxdf_batch": [vp, vp, C.c_int64, vp],
         "spt_render": [vp, P(RenderDesc), vp, vp, P(Stats)],
         "spt_render_device": [vp, P(RenderDesc), vp, P(Stats)],
+        "spt_owned_tiles": [C.c_int32] * 6 + [vp, C.c_int64, P(C.c_int64)],
     }
     for name, args in sig.items():
         fn = getattr(lib, name)

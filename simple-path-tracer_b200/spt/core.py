@@ -107,3 +107,13 @@ class Scene:
         st = abi.Stats()
         abi.check(self.lib, self.lib.spt_render_device(self.h, C.byref(rd), d_out_ptr, C.byref(st)))
         return st.as_dict()
+
+
+def owned_tiles(width, height, rank, world_size, tile=(0, 0)):
+    """spt_owned_tiles: host-only, works without a GPU."""
+    lib = abi.load_library()
+    n = C.c_int64()
+    abi.check(lib, lib.spt_owned_tiles(width, height, tile[0], tile[1], rank, world_size, None, 0, C.byref(n)))
+    out = np.zeros(max(1, n.value), np.uint32)
+    abi.check(lib, lib.spt_owned_tiles(width, height, tile[0], tile[1], rank, world_size, out.ctypes.data, n.value, C.byref(n)))
+    return out[:n.value]
