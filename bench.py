@@ -1,0 +1,260 @@
+"""bench.py — measures BASELINE.json's metric (Mpaths/s, with Mrays/s alongside) for the wavefront path-tracing core.
+
+    python bench.py --gpus N --steps K --warmup W            (N>1: launched by torchrun, one rank per GPU)
+    python bench.py --impl reference ...                     (the CPU restatement of the reference, all host threads)
+
+One "step" = one full render of the workload (default: C2 = bunny_5k conductor/PBR scene, 1920x1080 @ 256 spp,
+max_depth 8, recurrence sampler, box r=0.5 — BASELINE.json configs[1]).  `value` is measured with the scene resident
+in HBM and the framebuffer left on the device; `e2e` goes through spt_render with host buffers and re-sends the
+flattened scene from pinned memory every step.  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (os.path.join(ROOT, "simple-path-tracer_b200"), ROOT):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return json.load(fh), "measured"
+    except OSError:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index=0):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(self.rows)}
+
+
+def workload(args):
+    from spt import scenes
+    cfg = dict(scenes.CONFIGS[args.workload])
+    w = args.width or cfg["width"]
+    h = args.height or cfg["height"]
+    spp = args.spp or cfg["spp"]
+    return cfg, w, h, spp
+
+
+def run_reference(args):
+    """The reference arm: the reference's own CPU algorithm (oracle restatement — the Rust binary cannot be built here)
+    on the box's host cores, reference-faithful mode (its BVH, its per-thread RNG/sampler discipline, 2 x cores threads)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import orc
+    from spt import scenes
+    cfg, w, h, spp = workload(args)
+    fs = scenes.load(args.workload)
+    osc = orc.OracleScene(fs)
+    cores = os.cpu_count() or 1
+    # bounded sample of the same workload: same scene/camera/depth/sampler at reduced resolution and spp, sized by a probe
+    sw, sh = max(16, w // 12), max(9, h // 12)
+    t = time.time(); _, st = osc.render(sw, sh, spp=1, rng_mode=0); probe = time.time() - t
+    per_path = probe / max(1, st["paths"])
+    sspp = int(max(1, min(spp, args.ref_seconds / max(per_path * sw * sh, 1e-9))))
+    for _ in range(args.warmup if args.warmup < 2 else 1):
+        osc.render(sw, sh, spp=max(1, sspp // 8), rng_mode=0)
+    times, paths, rays = [], 0, 0
+    for k in range(args.steps):
+        t = time.time(); _, st = osc.render(sw, sh, spp=sspp, rng_mode=0, seed=k + 1); times.append(time.time() - t)
+        paths += st["paths"]; rays += st["ext_rays"] + st["shadow_rays"] + st["probe_rays"]
+    total = sum(times)
+    v = paths / total / 1e6
+    sample = f"{args.workload} scene at {sw}x{sh} @ {sspp} spp per step (full config: {w}x{h} @ {spp} spp), reference BVH + per-thread RNG, {2 * cores} threads"
+    print(json.dumps({
+        "impl": "reference", "metric": "Mpaths/s", "value": v, "unit": "Mpaths/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {w}x{h} @ {spp} spp, max_depth 8", "sampler": "recurrence"},
+        "mrays_per_s": rays / total / 1e6,
+        "cpu_baseline": {"value": v, "unit": "Mpaths/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2")
+    ap.add_argument("--width", type=int, default=0)
+    ap.add_argument("--height", type=int, default=0)
+    ap.add_argument("--spp", type=int, default=0)
+    ap.add_argument("--pool", type=int, default=0)
+    ap.add_argument("--ref-seconds", type=float, default=8.0, help="CPU seconds per reference/cpu_baseline step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from spt import abi, core, scenes
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:
+        torch.cuda.set_device(local)
+    W = max(3, args.warmup)
+    cfg, w, h, spp = workload(args)
+    fs = scenes.load(args.workload)
+    ctx = core.Context(local)
+    sc = core.Scene(ctx, fs)
+    info = sc.info()
+    dev = torch.device("cuda", local)
+    fb = torch.zeros((h, w, 3), dtype=torch.float32, device=dev)
+    kw = dict(spp=spp, max_depth=8, sampler="recurrence", rank=rank, world_size=world, pool_size=args.pool)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(seed, flags=0):
+        st = sc.render_device(fb.data_ptr(), w, h, seed=seed, flags=flags, **kw)
+        if world > 1:
+            dist.reduce(fb, dst=0, op=dist.ReduceOp.SUM)  # framebuffer gather over NVLink (disjoint tiles: exact)
+        return st
+
+    for i in range(W):
+        step(100 + i)
+    # ---- timed region: device-resident inputs and outputs
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    barrier()
+    t0 = time.perf_counter()
+    stats = [step(i + 1, abi.RENDER_TIME_STAGES) for i in range(args.steps)]
+    barrier()
+    elapsed = time.perf_counter() - t0
+    tt = torch.tensor([elapsed], dtype=torch.float64, device=dev)
+    agg = torch.tensor([sum(s[k] for s in stats) for k in ("paths", "ext_rays", "shadow_rays", "probe_rays", "kernel_launches")],
+                       dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dist.all_reduce(agg, op=dist.ReduceOp.SUM)
+    elapsed = float(tt.item())
+    paths, ext, shadow, probe, launches = (float(x) for x in agg.tolist())
+    value = paths / elapsed / 1e6
+    mrays = (ext + shadow + probe) / elapsed / 1e6
+
+    # ---- e2e: host buffers in and out (scene re-sent from pinned memory, framebuffer read back) every step
+    e2e_t0 = time.perf_counter()
+    h2d = 0
+    for i in range(args.steps):
+        h2d = sc.upload()
+        if world > 1:
+            step(i + 1)
+            if rank == 0:
+                host = fb.cpu()
+        else:
+            img, _ = sc.render(w, h, seed=i + 1, **{k: v for k, v in kw.items()})
+    barrier()
+    e2e_elapsed = time.perf_counter() - e2e_t0
+    te = torch.tensor([e2e_elapsed], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = paths / float(te.item()) / 1e6
+    if sampler:
+        sampler.stop_flag = True
+        sampler.join(timeout=2)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    # ---- roofline of the dominant kernel (extend = closest-hit traversal), rank 0
+    peaks, peak_src = load_peaks()
+    cst = sc.render_device(fb.data_ptr(), w, h, seed=1, flags=abi.RENDER_COUNT_TRAVERSAL,
+                           **dict(kw, spp=max(1, min(spp, 8))))
+    n_rays = cst["ext_rays"] + cst["shadow_rays"] + cst["probe_rays"]
+    n_node, n_tri, n_inst = cst["nodes_visited"] / n_rays, cst["tris_tested"] / n_rays, cst["insts_visited"] / n_rays
+    b_ray = 52.0 + 80.0 * n_node + 48.0 * n_tri + 64.0 * n_inst          # SURVEY §8d algorithmic bytes per traced ray
+    s0 = stats[-1]
+    ext_launches = s0["iterations"]
+    ext_seconds = s0["seconds_stage"][1]
+    rays_per_launch = s0["ext_rays"] / max(1, ext_launches)
+    achieved = rays_per_launch * b_ray / max(ext_seconds / max(1, ext_launches), 1e-12) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_src,
+                "bytes_per_ray": b_ray, "nodes_per_ray": n_node, "tris_per_ray": n_tri, "insts_per_ray": n_inst,
+                "rays_per_launch": rays_per_launch, "avg_launch_ms": 1e3 * ext_seconds / max(1, ext_launches),
+                "stage_seconds": {"extend": s0["seconds_stage"][1], "shade": s0["seconds_stage"][2], "connect": s0["seconds_stage"][3],
+                                  "total": s0["seconds_total"]},
+                "note": "scene working set (%.2f MB) is L2-resident: the HBM figure is the contract's denominator, the binding roof is L2/latency" % (info["bytes_total"] / 1e6)}
+    out = {
+        "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": W,
+        "ms_per_step": 1e3 * elapsed / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {w}x{h} @ {spp} spp, max_depth 8, recurrence sampler, box r=0.5",
+                   "scene": "bunny_5k x3 (conductor, pbr_metallic iso+aniso) + room + emissive quad, power_is MIS" if args.workload == "c2" else args.workload,
+                   "parallelism": f"tiles{world}", "pool_slots": s0 and (args.pool or 1 << 20),
+                   "l2_policy": "per-step working set (path pool 143 MB + film) exceeds L2; no explicit flush"},
+        "mrays_per_s": mrays, "rays_per_path": (ext + shadow + probe) / paths,
+        "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(w * h * 3 * 4)},
+        "gpu_launches": int(launches), "roofline": roofline, "clocks": sampler.summary() if sampler else None,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import orc
+        osc = orc.OracleScene(fs)
+        cores = os.cpu_count() or 1
+        sw, sh = max(16, w // 12), max(9, h // 12)
+        t = time.time(); _, st = osc.render(sw, sh, spp=1, rng_mode=0); probe_t = time.time() - t
+        sspp = int(max(1, min(spp, 15.0 / max(probe_t, 1e-6))))
+        t = time.time(); _, st = osc.render(sw, sh, spp=sspp, rng_mode=0); dt = time.time() - t
+        out["cpu_baseline"] = {"value": st["paths"] / dt / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "port",
+                               "sample": f"{args.workload} scene at {sw}x{sh} @ {sspp} spp ({st['paths']} paths, {dt:.1f} s), reference BVH + per-thread RNG, {2 * cores} threads",
+                               "mrays_per_s": (st["ext_rays"] + st["shadow_rays"] + st["probe_rays"]) / dt / 1e6}
+    print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -91,6 +91,7 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
   if (d.n_cameras <= 0) return bad("At least one camera is needed");
   // ---- textures (+ mip pyramids) -----------------------------------------------------------------------------
   hs.textures.resize(d.n_textures);
+  std::vector<int> tex_depth(std::max(1, d.n_textures), 0); // nesting of binary operators (device limit: 3)
   for (int i = 0; i < d.n_textures; i++) {
     const SptTextureDesc& t = d.textures[i];
     DTexture o; memset(&o, 0, sizeof(o));
@@ -127,6 +128,9 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
         cur.swap(nxt); w = nw; h = nh;
       }
     }
+    if (t.tag >= SPT_TEX_ADD && t.tag <= SPT_TEX_DIV) tex_depth[i] = 1 + std::max(tex_depth[t.child[0]], tex_depth[t.child[1]]);
+    else if (t.tag >= SPT_TEX_SRGB) tex_depth[i] = tex_depth[t.child[0]];
+    if (tex_depth[i] > 3) return bad("texture: more than 3 nested binary operators are not supported");
     hs.textures[i] = o;
   }
   auto tex_ok = [&](int id) { return id >= 0 && id < d.n_textures; };

@@ -3,6 +3,9 @@
 #include "wavefront.cuh"
 
 #define SPT_BLOCK 128
+#ifndef SPT_SHADE_MINB
+#define SPT_SHADE_MINB 1
+#endif
 
 // ---- extend: closest hit for every live path (pt.rs:49-50) ---------------------------------------------------
 template <bool COUNT>
@@ -43,7 +46,7 @@ __global__ void __launch_bounds__(SPT_BLOCK) k_connect(const DScene sc, const Re
 
 // ---- shade (+ regenerate): one iteration of the body of trace_ray's loop, pt.rs:48-207 --------------------------
 template <bool COUNT>
-__global__ void __launch_bounds__(SPT_BLOCK) k_shade(const DScene sc, const RenderParams P) {
+__global__ void __launch_bounds__(SPT_BLOCK, SPT_SHADE_MINB) k_shade(const DScene sc, const RenderParams P) {
   uint32_t nonfinite = 0, n_probe = 0, n_new = 0, n_live = 0;
   TravCounters tc = {0, 0, 0};
   for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < P.pool.n; slot += gridDim.x * blockDim.x) {

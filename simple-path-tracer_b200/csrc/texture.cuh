@@ -93,37 +93,40 @@ SPT_D TexIn tex_modify(const DTexture& t, const TexIn& in) { // input_modifier.r
   return o;
 }
 
-// Evaluates the texture as RGBA (alpha = 1 for scalars, scalar.rs:26-33).  The expression tree is walked with a
-// small explicit stack: operators are binary, so post-order evaluation needs one value per pending left operand.
-// Trees in the shipped scenes are 1-3 nodes deep; depth is bounded at 8.
-__device__ __noinline__ float4 tex_eval(const DScene& sc, int id, TexIn in) {
-  // Fast path: scalar (every benchmark scene)
-  {
-    const DTexture& t = sc.textures[id];
-    if (t.tag == 0) return make_float4(t.value[0], t.value[1], t.value[2], 1.0f);
-  }
-  // General path: recursion-free evaluation.  Unary wrappers (srgb, modifier) are peeled iteratively; binary
-  // operators evaluate their right subtree by a bounded recursive call.
+// Evaluates the texture as RGBA (alpha = 1 for scalars, scalar.rs:26-33).  Unary wrappers (sRGB, input modifier) are
+// peeled iteratively; a binary operator evaluates its two children with the next-lower template depth, so there is
+// no device recursion and the stack frame is known statically.  SPT_TEX_MAX_DEPTH nested binary operators are
+// supported (the host flattener rejects deeper trees); every shipped scene needs at most 2.
+#define SPT_TEX_MAX_DEPTH 3
+template <int D>
+__device__ __noinline__ float4 tex_eval_d(const DScene& sc, int id, TexIn in) {
   bool srgb = false;
   for (int guard = 0; guard < 8; guard++) {
     const DTexture& t = sc.textures[id];
-    if (t.tag == 6) { srgb = !srgb ? true : srgb; id = t.child0; continue; }
+    if (t.tag == 6) { srgb = true; id = t.child0; continue; }
     if (t.tag == 7) { in = tex_modify(t, in); id = t.child0; continue; }
     break;
   }
   const DTexture& t = sc.textures[id];
-  float4 r;
+  float4 r = make_float4(0, 0, 0, 0);
   if (t.tag == 0) r = make_float4(t.value[0], t.value[1], t.value[2], 1.0f);
   else if (t.tag == 1) { const float2 uv = texin_wrapped(in); r = tex_trilinear(sc, t, uv.x, uv.y, in.duvdx, in.duvdy); }
   else if (t.tag >= 2 && t.tag <= 5) {
-    const float4 a = tex_eval(sc, t.child0, in), b = tex_eval(sc, t.child1, in);
-    if (t.tag == 2) r = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
-    else if (t.tag == 3) r = make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w);
-    else if (t.tag == 4) r = make_float4(a.x * b.x, a.y * b.y, a.z * b.z, a.w * b.w);
-    else r = make_float4(a.x / b.x, a.y / b.y, a.z / b.z, a.w / b.w);
-  } else r = make_float4(0, 0, 0, 0);
+    if constexpr (D > 0) {
+      const float4 a = tex_eval_d<D - 1>(sc, t.child0, in), b = tex_eval_d<D - 1>(sc, t.child1, in);
+      if (t.tag == 2) r = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+      else if (t.tag == 3) r = make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w);
+      else if (t.tag == 4) r = make_float4(a.x * b.x, a.y * b.y, a.z * b.z, a.w * b.w);
+      else r = make_float4(a.x / b.x, a.y / b.y, a.z / b.z, a.w / b.w);
+    }
+  }
   if (srgb) r = make_float4(srgb_lin(r.x), srgb_lin(r.y), srgb_lin(r.z), r.w);
   return r;
+}
+SPT_D float4 tex_eval(const DScene& sc, int id, const TexIn& in) {
+  const DTexture& t = sc.textures[id];
+  if (t.tag == 0) return make_float4(t.value[0], t.value[1], t.value[2], 1.0f); // fast path: every benchmark scene
+  return tex_eval_d<SPT_TEX_MAX_DEPTH>(sc, id, in);
 }
 SPT_D float3 tex_color(const DScene& sc, int id, const TexIn& in) { return mk3(tex_eval(sc, id, in)); }
 SPT_D float tex_float(const DScene& sc, int id, const TexIn& in, int chan) {

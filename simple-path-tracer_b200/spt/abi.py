@@ -148,7 +148,7 @@ def load_library(path=None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    path = path or LIB_PATH
+    path = path or os.environ.get("SPT_LIB") or LIB_PATH  # SPT_LIB: A/B builds of the same library while tuning
     if not os.path.exists(path):
         raise SptError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
                        "(the product has no CPU fallback)")
