@@ -31,6 +31,30 @@ struct BsdfSample {
   bool need_probe; // substrate is Subsurface: the caller must trace the probe ray and call bsdf_finish_probe()
 };
 
+
+// Compile-time narrowing by material class: shade kernels are instantiated per material tag MAT (SPT_MAT_*), which
+// fixes the Fresnel model and the substrate and leaves at most two Bxdf variants; MAT = -1 keeps everything dynamic.
+template <int MAT> SPT_D int tag_of(const Bsdf& b) {
+  if (MAT == 0) return BX_LAMBERT;
+  if (MAT == 1) return BX_PSEUDO;
+  if (MAT == 2) return b.tag == BX_MF_CONDUCTOR ? BX_MF_CONDUCTOR : BX_SP_CONDUCTOR;
+  if (MAT == 3) return b.tag == BX_MF_DIELECTRIC ? BX_MF_DIELECTRIC : BX_SP_DIELECTRIC;
+  if (MAT >= 4) return b.tag == BX_MF_PLASTIC ? BX_MF_PLASTIC : BX_SP_PLASTIC;
+  return b.tag;
+}
+template <int MAT> SPT_D int fr_of(const Bsdf& b) {
+  if (MAT == 2) return FR_CONDUCTOR;
+  if (MAT == 5 || MAT == 6) return FR_SCHLICK;
+  if (MAT >= 0) return FR_DIELECTRIC;
+  return b.fr;
+}
+template <int MAT> SPT_D int sub_of(const Bsdf& b) {
+  if (MAT == 4) return SUB_DIFFUSE;
+  if (MAT == 7) return SUB_SUBSURFACE;
+  if (MAT >= 0) return SUB_LAMBERT;
+  return b.sub;
+}
+
 // ---- bxdf/util.rs ---------------------------------------------------------------------------------------
 SPT_D float3 refl_z(float3 i) { return mk3(-i.x, -i.y, i.z); }
 SPT_D float3 refl_n(float3 i, float3 n) { return (2.0f * dot3(i, n)) * n - i; }
@@ -102,8 +126,8 @@ SPT_D float3 vndf_sample(float3 ve, float ax, float ay, float u0, float u1, floa
   const float l2 = vh.x * vh.x + vh.y * vh.y;
   const float3 T1 = l2 > 0.f ? mk3(-vh.y, vh.x, 0.f) / sqrtf(l2) : mk3(1, 0, 0);
   const float3 T2 = cross3(vh, T1);
-  const float r = sqrtf(u0), phi = 2.0f * SPT_PI * u1;
-  float sp, cp; sincosf(phi, &sp, &cp);
+  const float r = sqrtf(u0);
+  float sp, cp; sincos_2pi(u1, sp, cp);
   const float t1 = r * cp; float t2 = r * sp;
   const float s = 0.5f * (1.0f + vh.z);
   t2 = (1.0f - s) * sqrtf(1.0f - t1 * t1) + s * t2;
@@ -113,21 +137,20 @@ SPT_D float3 vndf_sample(float3 ve, float ax, float ay, float u0, float u1, floa
   return ne;
 }
 SPT_D float3 cosine_hemisphere(float u0, float u1) { // Rng::cosine_weighted_on_hemisphere, core/rng.rs:72-80
-  const float phi = u0 * 2.0f * SPT_PI;
-  float sp, cp; sincosf(phi, &sp, &cp);
+  float sp, cp; sincos_2pi(u0, sp, cp);
   const float st = sqrtf(u1), ct = sqrtf(1.0f - u1);
   return mk3(st * cp, st * sp, ct);
 }
 
 // ---- Fresnel dispatch (bxdf/fresnel.rs) -------------------------------------------------------------------
-SPT_D float3 bsdf_fresnel(const Bsdf& b, float3 i, float3 n) {
-  if (b.fr == FR_DIELECTRIC) return mk3(fresnel_diel(b.ior, i, n));
-  if (b.fr == FR_CONDUCTOR) return fresnel_cond(b.c0, b.c1, i, n);
+template <int MAT> SPT_D float3 bsdf_fresnel(const Bsdf& b, float3 i, float3 n) {
+  if (fr_of<MAT>(b) == FR_DIELECTRIC) return mk3(fresnel_diel(b.ior, i, n));
+  if (fr_of<MAT>(b) == FR_CONDUCTOR) return fresnel_cond(b.c0, b.c1, i, n);
   return b.c0 + (mk3(1.f) - b.c0) * pow5f(1.0f - dot3(i, n)); // schlick_fresnel_with_r0 :120-122
 }
-SPT_D float bsdf_fresnel_ior(const Bsdf& b) { // FresnelT::ior
-  if (b.fr == FR_DIELECTRIC) return b.ior;
-  if (b.fr == FR_CONDUCTOR) return 1.0f;
+template <int MAT> SPT_D float bsdf_fresnel_ior(const Bsdf& b) { // FresnelT::ior
+  if (fr_of<MAT>(b) == FR_DIELECTRIC) return b.ior;
+  if (fr_of<MAT>(b) == FR_CONDUCTOR) return 1.0f;
   const float s = sqrtf(lum3(b.c0));
   return (1.0f - s) / (1.0f + s);
 }
@@ -135,16 +158,16 @@ SPT_D float ndf_vis(const Bsdf& b, float3 wo, float3 wi, float3 h) { return ggx_
 
 // ---- substrates (bxdf/substrate.rs) -------------------------------------------------------------------------
 SPT_D float sub_pdf(float3 wo, float3 wi) { return wo.z * wi.z >= 0.f ? fabsf(wi.z) * SPT_INV_PI : 1.0f; }
-SPT_D float3 sub_eval(const Bsdf& b, float3 wo, float3 wi) {
+template <int MAT> SPT_D float3 sub_eval(const Bsdf& b, float3 wo, float3 wi) {
   if (!(wo.z * wi.z >= 0.f)) return mk3(0.f);
-  if (b.sub == SUB_LAMBERT) return b.s_refl * SPT_INV_PI;
+  if (sub_of<MAT>(b) == SUB_LAMBERT) return b.s_refl * SPT_INV_PI;
   return (1.0f - fresnel_diel(b.s_ior, wi, mk3(0, 0, 1))) * b.s_base; // Diffuse::bxdf :169-176 (Subsurface delegates, :345-347)
 }
-SPT_D void sub_sample_diffuse(const Bsdf& b, float3 wo, DrawSrc& rng, float3& wi, float3& f, float& pdf) { // :141-160, lambert.rs:20-36
+template <int MAT, class RNG> SPT_D void sub_sample_diffuse(const Bsdf& b, float3 wo, RNG& rng, float3& wi, float3& f, float& pdf) { // :141-160, lambert.rs:20-36
   const float u0 = rng.next(), u1 = rng.next();
   wi = cosine_hemisphere(u0, u1);
   if (wo.z < 0.f) wi.z = -wi.z;
-  f = b.sub == SUB_LAMBERT ? b.s_refl * SPT_INV_PI : (1.0f - fresnel_diel(b.s_ior, wi, mk3(0, 0, 1))) * b.s_base;
+  f = sub_of<MAT>(b) == SUB_LAMBERT ? b.s_refl * SPT_INV_PI : (1.0f - fresnel_diel(b.s_ior, wi, mk3(0, 0, 1))) * b.s_base;
   pdf = fabsf(wi.z) * SPT_INV_PI;
 }
 SPT_D float3 ss_sp(const Bsdf& b, float r) { // Subsurface::sp :211-215
@@ -152,7 +175,7 @@ SPT_D float3 ss_sp(const Bsdf& b, float r) { // Subsurface::sp :211-215
   return (e1 + e2) * SPT_INV_PI / ((8.0f * b.s_d) * r);
 }
 
-SPT_D bool bsdf_is_delta(const Bsdf& b) { return b.tag == BX_PSEUDO || b.tag == BX_SP_CONDUCTOR || b.tag == BX_SP_DIELECTRIC; }
+template <int MAT> SPT_D bool bsdf_is_delta(const Bsdf& b) { const int t = tag_of<MAT>(b); return t == BX_PSEUDO || t == BX_SP_CONDUCTOR || t == BX_SP_DIELECTRIC; }
 
 SPT_D float plastic_reflect_pdf(const Bsdf& b, float3 fres) {
   const float sw = lum3(fres), bw = lum3((mk3(1.f) - fres) * b.s_refl);
@@ -160,10 +183,10 @@ SPT_D float plastic_reflect_pdf(const Bsdf& b, float3 fres) {
 }
 
 // BxdfT::pdf
-SPT_D float bsdf_pdf(const Bsdf& b, float3 wo, float3 wi) {
+template <int MAT> SPT_D float bsdf_pdf(const Bsdf& b, float3 wo, float3 wi) {
   const float3 Z = mk3(0, 0, 1);
   const bool same = wo.z * wi.z >= 0.f;
-  switch (b.tag) {
+  switch (tag_of<MAT>(b)) {
     case BX_LAMBERT: return same ? fabsf(wi.z) * SPT_INV_PI : 1.0f; // lambert.rs:38-44
     case BX_PSEUDO: case BX_SP_CONDUCTOR: return 1.0f;
     case BX_MF_CONDUCTOR: { // microfacet_conductor.rs:44-53
@@ -174,47 +197,47 @@ SPT_D float bsdf_pdf(const Bsdf& b, float3 wo, float3 wi) {
     case BX_MF_DIELECTRIC: { // microfacet_dielectric.rs:93-116
       if (same) {
         const float3 h = half_refl(wo, wi);
-        return lum3(bsdf_fresnel(b, wo, h)) * vndf_pdf(h, wo, b.ax, b.ay) / (4.0f * fabsf(dot3(wo, h)));
+        return lum3(bsdf_fresnel<MAT>(b, wo, h)) * vndf_pdf(h, wo, b.ax, b.ay) / (4.0f * fabsf(dot3(wo, h)));
       }
-      const float ior = bsdf_fresnel_ior(b);
+      const float ior = bsdf_fresnel_ior<MAT>(b);
       const float3 h = half_refr(wo, wi, ior);
-      const float rp = lum3(bsdf_fresnel(b, wo, h));
+      const float rp = lum3(bsdf_fresnel<MAT>(b, wo, h));
       const float ratio = wo.z >= 0.f ? 1.0f / ior : ior;
       const float den = sqr(ratio * dot3(wo, h) + dot3(wi, h));
       return (1.0f - rp) * vndf_pdf(h, wo, b.ax, b.ay) * fabsf(dot3(wi, h)) / den;
     }
     case BX_MF_PLASTIC: { // microfacet_plastic.rs:81-98
       if (!same) return 1.0f;
-      const float rp = plastic_reflect_pdf(b, bsdf_fresnel(b, wo, Z));
+      const float rp = plastic_reflect_pdf(b, bsdf_fresnel<MAT>(b, wo, Z));
       const float3 h = half_refl(wo, wi);
       return rp * vndf_pdf(h, wo, b.ax, b.ay) / (4.0f * fabsf(dot3(wo, h))) + (1.0f - rp) * sub_pdf(wo, wi);
     }
-    case BX_SP_DIELECTRIC: { const float rp = lum3(bsdf_fresnel(b, wo, Z)); return same ? rp : 1.0f - rp; } // specular_dielectric.rs:75-83
+    case BX_SP_DIELECTRIC: { const float rp = lum3(bsdf_fresnel<MAT>(b, wo, Z)); return same ? rp : 1.0f - rp; } // specular_dielectric.rs:75-83
     default: { // BX_SP_PLASTIC, specular_plastic.rs:63-77
       if (!same) return 1.0f;
-      const float rp = plastic_reflect_pdf(b, bsdf_fresnel(b, wo, Z));
+      const float rp = plastic_reflect_pdf(b, bsdf_fresnel<MAT>(b, wo, Z));
       return rp + (1.0f - rp) * sub_pdf(wo, wi);
     }
   }
 }
 
 // BxdfT::bxdf
-SPT_D float3 bsdf_eval(const Bsdf& b, float3 wo, float3 wi) {
+template <int MAT> SPT_D float3 bsdf_eval(const Bsdf& b, float3 wo, float3 wi) {
   const float3 Z = mk3(0, 0, 1), K = mk3(0.f), W = mk3(1.f);
   const bool same = wo.z * wi.z >= 0.f;
-  switch (b.tag) {
+  switch (tag_of<MAT>(b)) {
     case BX_LAMBERT: return same ? b.c0 * SPT_INV_PI : K;
     case BX_PSEUDO: return dot3(wo, wi) < -0.999f ? W / fabsf(wi.z) : K; // pseudo.rs:32-38
     case BX_MF_CONDUCTOR: {
       if (!same) return K;
       const float3 h = half_refl(wo, wi);
-      return bsdf_fresnel(b, wo, h) * ndf_vis(b, wo, wi, h);
+      return bsdf_fresnel<MAT>(b, wo, h) * ndf_vis(b, wo, wi, h);
     }
     case BX_MF_DIELECTRIC: { // :118-141
-      if (same) { const float3 h = half_refl(wo, wi); return bsdf_fresnel(b, wo, h) * ndf_vis(b, wo, wi, h); }
-      const float ior = bsdf_fresnel_ior(b);
+      if (same) { const float3 h = half_refl(wo, wi); return bsdf_fresnel<MAT>(b, wo, h) * ndf_vis(b, wo, wi, h); }
+      const float ior = bsdf_fresnel_ior<MAT>(b);
       const float3 h = half_refr(wo, wi, ior);
-      const float3 f = bsdf_fresnel(b, wo, h);
+      const float3 f = bsdf_fresnel<MAT>(b, wo, h);
       const float ratio = wo.z >= 0.f ? 1.0f / ior : ior;
       const float den = sqr(ratio * dot3(wo, h) + dot3(wi, h));
       const float num = 4.0f * fabsf(dot3(wo, h)) * fabsf(dot3(wi, h));
@@ -223,13 +246,13 @@ SPT_D float3 bsdf_eval(const Bsdf& b, float3 wo, float3 wi) {
     case BX_MF_PLASTIC: { // :100-114
       if (!same) return K;
       const float3 h = half_refl(wo, wi);
-      return bsdf_fresnel(b, wo, h) * ndf_vis(b, wo, wi, h) + (W - bsdf_fresnel(b, wo, Z)) * sub_eval(b, wo, wi);
+      return bsdf_fresnel<MAT>(b, wo, h) * ndf_vis(b, wo, wi, h) + (W - bsdf_fresnel<MAT>(b, wo, Z)) * sub_eval<MAT>(b, wo, wi);
     }
-    case BX_SP_CONDUCTOR: return dot3(wi, refl_z(wo)) > 0.999f ? bsdf_fresnel(b, wo, Z) / fabsf(wi.z) : K; // :43-50
+    case BX_SP_CONDUCTOR: return dot3(wi, refl_z(wo)) > 0.999f ? bsdf_fresnel<MAT>(b, wo, Z) / fabsf(wi.z) : K; // :43-50
     case BX_SP_DIELECTRIC: { // :85-106
-      const float3 f = bsdf_fresnel(b, wo, Z);
+      const float3 f = bsdf_fresnel<MAT>(b, wo, Z);
       if (same) return dot3(wi, refl_z(wo)) > 0.999f ? f / fabsf(wi.z) : K;
-      const float ior = bsdf_fresnel_ior(b);
+      const float ior = bsdf_fresnel_ior<MAT>(b);
       float3 e;
       if (refr_z(wo, ior, e) && dot3(wi, e) > 0.999f) {
         const float ratio = wo.z >= 0.f ? 1.0f / ior : ior;
@@ -239,23 +262,23 @@ SPT_D float3 bsdf_eval(const Bsdf& b, float3 wo, float3 wi) {
     }
     default: { // BX_SP_PLASTIC :79-89
       if (!same) return K;
-      const float3 f = bsdf_fresnel(b, wo, Z);
-      return f / fabsf(wi.z) + (W - f) * sub_eval(b, wo, wi);
+      const float3 f = bsdf_fresnel<MAT>(b, wo, Z);
+      return f / fabsf(wi.z) + (W - f) * sub_eval<MAT>(b, wo, wi);
     }
   }
 }
 
 // Combination step shared by MicrofacetPlastic / SpecularPlastic when the substrate was sampled
 // (microfacet_plastic.rs:59-78, specular_plastic.rs:46-60): adds the specular lobe's value and pdf at samp.wi.
-SPT_D void plastic_combine(const Bsdf& b, float3 wo, float3 wi, float3 fsub, float psub, int lobe, BsdfSample& s) {
+template <int MAT> SPT_D void plastic_combine(const Bsdf& b, float3 wo, float3 wi, float3 fsub, float psub, int lobe, BsdfSample& s) {
   const float3 Z = mk3(0, 0, 1), W = mk3(1.f);
-  const float3 fm = bsdf_fresnel(b, wo, Z);
+  const float3 fm = bsdf_fresnel<MAT>(b, wo, Z);
   const float rp = plastic_reflect_pdf(b, fm);
   s.wi = wi; s.lobe = lobe; s.dir = DIR_REFLECT;
-  if (b.tag == BX_MF_PLASTIC) {
+  if (tag_of<MAT>(b) == BX_MF_PLASTIC) {
     const float3 h = half_refl(wo, wi);
     const float spdf = rp * vndf_pdf(h, wo, b.ax, b.ay) / (4.0f * fabsf(dot3(wo, h)));
-    s.f = (W - fm) * fsub + bsdf_fresnel(b, wo, h) * ndf_vis(b, wo, wi, h);
+    s.f = (W - fm) * fsub + bsdf_fresnel<MAT>(b, wo, h) * ndf_vis(b, wo, wi, h);
     s.pdf = (1.0f - rp) * psub + spdf;
   } else {
     s.f = (W - fm) * fsub + fm / fabsf(wi.z);
@@ -264,10 +287,10 @@ SPT_D void plastic_combine(const Bsdf& b, float3 wo, float3 wi, float3 fsub, flo
 }
 
 // BxdfT::sample.  Random numbers are consumed in the reference's order.
-SPT_D void bsdf_sample(const Bsdf& b, float3 wo, DrawSrc& rng, BsdfSample& s) {
+template <int MAT, class RNG> SPT_D void bsdf_sample(const Bsdf& b, float3 wo, RNG& rng, BsdfSample& s) {
   const float3 Z = mk3(0, 0, 1), W = mk3(1.f);
   s.need_probe = false;
-  switch (b.tag) {
+  switch (tag_of<MAT>(b)) {
     case BX_LAMBERT: { // lambert.rs:20-36
       const float u0 = rng.next(), u1 = rng.next();
       float3 wi = cosine_hemisphere(u0, u1);
@@ -282,16 +305,16 @@ SPT_D void bsdf_sample(const Bsdf& b, float3 wo, DrawSrc& rng, BsdfSample& s) {
       const float u0 = rng.next(), u1 = rng.next();
       float hp; const float3 h = vndf_sample(wo, b.ax, b.ay, u0, u1, hp);
       const float3 wi = refl_n(wo, h);
-      s.wi = wi; s.f = bsdf_fresnel(b, wo, h) * ndf_vis(b, wo, wi, h); s.pdf = hp / (4.0f * fabsf(dot3(wo, h)));
+      s.wi = wi; s.f = bsdf_fresnel<MAT>(b, wo, h) * ndf_vis(b, wo, wi, h); s.pdf = hp / (4.0f * fabsf(dot3(wo, h)));
       s.lobe = LOBE_GLOSSY; s.dir = DIR_REFLECT;
       return;
     }
     case BX_MF_DIELECTRIC: { // microfacet_dielectric.rs:23-91
       const float u0 = rng.next(), u1 = rng.next();
       float hp; const float3 h = vndf_sample(wo, b.ax, b.ay, u0, u1, hp);
-      const float3 f = bsdf_fresnel(b, wo, h);
+      const float3 f = bsdf_fresnel<MAT>(b, wo, h);
       const float rp = lum3(f);
-      const float ior = bsdf_fresnel_ior(b);
+      const float ior = bsdf_fresnel_ior<MAT>(b);
       float3 wi;
       s.lobe = LOBE_GLOSSY;
       if (rng.next() < rp) {
@@ -308,13 +331,13 @@ SPT_D void bsdf_sample(const Bsdf& b, float3 wo, DrawSrc& rng, BsdfSample& s) {
     }
     case BX_SP_CONDUCTOR: { // specular_conductor.rs:19-37
       const float3 wi = refl_z(wo);
-      s.wi = wi; s.f = bsdf_fresnel(b, wo, Z) / fabsf(wi.z); s.pdf = 1.0f; s.lobe = LOBE_SPECULAR; s.dir = DIR_REFLECT;
+      s.wi = wi; s.f = bsdf_fresnel<MAT>(b, wo, Z) / fabsf(wi.z); s.pdf = 1.0f; s.lobe = LOBE_SPECULAR; s.dir = DIR_REFLECT;
       return;
     }
     case BX_SP_DIELECTRIC: { // specular_dielectric.rs:19-73
-      const float3 f = bsdf_fresnel(b, wo, Z);
+      const float3 f = bsdf_fresnel<MAT>(b, wo, Z);
       const float rp = lum3(f);
-      const float ior = bsdf_fresnel_ior(b);
+      const float ior = bsdf_fresnel_ior<MAT>(b);
       float3 wi;
       s.lobe = LOBE_SPECULAR;
       if (rng.next() < rp) { wi = refl_z(wo); s.wi = wi; s.f = f / fabsf(wi.z); s.pdf = rp; s.dir = DIR_REFLECT; }
@@ -325,28 +348,28 @@ SPT_D void bsdf_sample(const Bsdf& b, float3 wo, DrawSrc& rng, BsdfSample& s) {
       return;
     }
     default: { // BX_MF_PLASTIC (microfacet_plastic.rs:25-79) and BX_SP_PLASTIC (specular_plastic.rs:20-61)
-      const float3 fm = bsdf_fresnel(b, wo, Z);
+      const float3 fm = bsdf_fresnel<MAT>(b, wo, Z);
       const float rp = plastic_reflect_pdf(b, fm);
       if (rng.next() < rp) {
-        if (b.tag == BX_MF_PLASTIC) {
+        if (tag_of<MAT>(b) == BX_MF_PLASTIC) {
           const float u0 = rng.next(), u1 = rng.next();
           float hp; const float3 h = vndf_sample(wo, b.ax, b.ay, u0, u1, hp);
           const float3 wi = refl_n(wo, h);
           s.wi = wi; s.lobe = LOBE_GLOSSY; s.dir = DIR_REFLECT;
-          s.f = bsdf_fresnel(b, wo, h) * ndf_vis(b, wo, wi, h) + (W - fm) * sub_eval(b, wo, wi);
+          s.f = bsdf_fresnel<MAT>(b, wo, h) * ndf_vis(b, wo, wi, h) + (W - fm) * sub_eval<MAT>(b, wo, wi);
           s.pdf = rp * hp / (4.0f * fabsf(dot3(wo, h))) + (1.0f - rp) * sub_pdf(wo, wi);
         } else {
           const float3 wi = refl_z(wo);
           s.wi = wi; s.lobe = LOBE_SPECULAR; s.dir = DIR_REFLECT;
-          s.f = fm / fabsf(wi.z) + (W - fm) * sub_eval(b, wo, wi);
+          s.f = fm / fabsf(wi.z) + (W - fm) * sub_eval<MAT>(b, wo, wi);
           s.pdf = rp + (1.0f - rp) * sub_pdf(wo, wi);
         }
         return;
       }
-      if (b.sub == SUB_SUBSURFACE) { s.need_probe = true; s.wi = mk3(0.f); s.f = mk3(0.f); s.pdf = 1.0f; s.lobe = LOBE_DIFFUSE; s.dir = DIR_REFLECT; return; }
+      if (sub_of<MAT>(b) == SUB_SUBSURFACE) { s.need_probe = true; s.wi = mk3(0.f); s.f = mk3(0.f); s.pdf = 1.0f; s.lobe = LOBE_DIFFUSE; s.dir = DIR_REFLECT; return; }
       float3 wi, fs; float ps;
-      sub_sample_diffuse(b, wo, rng, wi, fs, ps);
-      plastic_combine(b, wo, wi, fs, ps, LOBE_DIFFUSE, s);
+      sub_sample_diffuse<MAT>(b, wo, rng, wi, fs, ps);
+      plastic_combine<MAT>(b, wo, wi, fs, ps, LOBE_DIFFUSE, s);
       return;
     }
   }
@@ -363,11 +386,11 @@ SPT_D void bsdf_set_diffuse_substrate(Bsdf& b, float3 refl, float ior) { // Diff
 }
 SPT_D float powi4(float x) { const float x2 = x * x; return x2 * x2; }
 
-SPT_D Bsdf make_bsdf(const DScene& sc, const DMaterial& m, const TexIn& in) {
+template <int MAT> SPT_D Bsdf make_bsdf(const DScene& sc, const DMaterial& m, const TexIn& in) {
   Bsdf b;
   b.tag = BX_LAMBERT; b.fr = FR_DIELECTRIC; b.sub = SUB_LAMBERT; b.ax = b.ay = 0.f; b.ior = m.ior;
   b.c0 = b.c1 = b.s_refl = b.s_base = b.s_d = mk3(0.f); b.s_ior = 1.f;
-  switch (m.tag) {
+  switch (MAT >= 0 ? MAT : m.tag) {
     case 0: b.c0 = tex_color(sc, m.tex[0], in); break; // lambert.rs:26-31
     case 1: b.tag = BX_PSEUDO; break;                   // pseudo.rs:20-24
     case 2: { // conductor.rs:50-73

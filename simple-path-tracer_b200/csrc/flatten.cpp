@@ -237,6 +237,7 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
     hs.inst[i] = o; hs.inst_shade[i] = sh;
   }
   // ---- TLAS, then lay the BLASes out behind it ---------------------------------------------------------------------------
+  std::vector<uint32_t> mesh_tri_base(std::max(1, d.n_meshes), 0u);
   std::vector<CwNode> tlas; std::vector<int> tlas_order;
   build_cwbvh(inst_box, 1, 0, 0, tlas, tlas_order, nullptr);
   hs.nodes = tlas; hs.tlas_nodes = (int64_t)tlas.size();
@@ -246,13 +247,43 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
     hs.meshes[mi].blas_root = (int32_t)node_base;
     for (CwNode n : blas_nodes[mi]) { n.child_base += node_base; n.prim_base += tri_base; hs.nodes.push_back(n); }
     const SptMeshDesc& m = d.meshes[mi];
+    mesh_tri_base[mi] = tri_base;
+    const float nz[3] = {0, 0, 1}, tx[3] = {1, 0, 0}, by[3] = {0, 1, 0}, uv0[2] = {0, 0};
     for (int t : blas_order[mi]) {
       float idf; int32_t id = t; memcpy(&idf, &id, 4);
-      for (int c = 0; c < 3; c++) { const float* p = m.position + 3 * m.index[3 * t + c]; hs.tris.push_back(make_float4(p[0], p[1], p[2], c == 0 ? idf : 0.f)); }
+      const float* P[3]; const float* N[3]; const float* T[3]; const float* B[3]; const float* UV[3];
+      for (int c = 0; c < 3; c++) {
+        const uint32_t vi = m.index[3 * t + c];
+        P[c] = m.position + 3 * vi;
+        N[c] = m.normal ? m.normal + 3 * vi : nz; UV[c] = m.texcoord ? m.texcoord + 2 * vi : uv0;
+        T[c] = m.tangent ? m.tangent + 3 * vi : tx; B[c] = m.bitangent ? m.bitangent + 3 * vi : by;
+        hs.tris.push_back(make_float4(P[c][0], P[c][1], P[c][2], c == 0 ? idf : 0.f));
+      }
+      // Triangle::pdf / BvhAccel::pdf: 1 / max(area, 1e-3) / n_tris (triangle.rs:272-280, bvh.rs:300-302, Q6)
+      const V3 e1{P[1][0] - P[0][0], P[1][1] - P[0][1], P[1][2] - P[0][2]}, e2{P[2][0] - P[0][0], P[2][1] - P[0][1], P[2][2] - P[0][2]};
+      const float area = length(cross(e1, e2)) * 0.5f;
+      const float prim_pdf = (1.0f / std::max(area, 0.001f)) / (float)m.n_tris;
+      const float w[9] = {UV[0][0], UV[0][1], UV[1][0], UV[1][1], UV[2][0], UV[2][1], prim_pdf, 0.f, 0.f};
+      for (int c = 0; c < 3; c++) hs.shade_tris.push_back(make_float4(N[c][0], N[c][1], N[c][2], w[c]));
+      for (int c = 0; c < 3; c++) hs.shade_tris.push_back(make_float4(T[c][0], T[c][1], T[c][2], w[3 + c]));
+      for (int c = 0; c < 3; c++) hs.shade_tris.push_back(make_float4(B[c][0], B[c][1], B[c][2], w[6 + c]));
     }
     hs.blas_nodes += (int64_t)blas_nodes[mi].size();
   }
-  for (int i = 0; i < d.n_instances; i++) if (hs.inst[i].kind == SPT_PRIM_TRIMESH) hs.inst[i].root = hs.meshes[hs.inst[i].mesh].blas_root;
+  hs.inst_mat.assign(std::max(1, d.n_instances), 0);
+  for (int i = 0; i < d.n_instances; i++) {
+    DInstance& I = hs.inst[i];
+    if (I.kind == SPT_PRIM_TRIMESH) {
+      const DMesh& dm = hs.meshes[I.mesh];
+      if (dm.n_tris <= SPT_SMALL_MESH) { I.kind = 2 | (dm.n_tris << 8); I.root = (int32_t)mesh_tri_base[I.mesh]; } // leaf triangles tested directly
+      else I.root = dm.blas_root;
+    }
+    const DSurface& sf = hs.surfaces[I.surface];
+    const int tag = hs.materials[sf.material].tag;
+    hs.inst_mat[i] = (uint8_t)tag;
+    hs.mat_mask |= 1u << tag;
+    if (sf.inside_medium >= 0 && !sf.double_sided) hs.has_medium = true;
+  }
   // ---- environment -----------------------------------------------------------------------------------------------------------
   float env_avg_power = 0.f;
   if (d.env) { // EnvLight::new, environment.rs:18-50 (Q7: theta lacks the factor pi)

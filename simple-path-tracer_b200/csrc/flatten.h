@@ -11,6 +11,10 @@ namespace spt {
 struct HostScene {
   std::vector<CwNode> nodes;        // TLAS first, then BLASes
   std::vector<float4> tris;         // 3 per triangle, BLAS leaf order
+  std::vector<float4> shade_tris;   // 9 per triangle, same order
+  std::vector<uint8_t> inst_mat;    // per instance: material tag
+  uint32_t mat_mask = 0;
+  bool has_medium = false;
   std::vector<int32_t> tlas_inst;
   std::vector<DInstance> inst;
   std::vector<DInstanceShade> inst_shade;

@@ -37,6 +37,12 @@ struct DrawSrc {
   }
 };
 
+// The draw source of the render kernels: just the 8-byte stream state.
+struct PathRng {
+  uint64_t state;
+  SPT_HD float next() { return rng_uniform(state); }
+};
+
 // Sub-pixel offsets of the additive-recurrence (R2) sampler, pixel_sampler/recurrence.rs:41-56, in closed form:
 // x_n = frac(0.5 + n*a1), y_n = frac(0.5 + n*a2) with 32-bit fixed-point a1 = 1/phi2, a2 = 1/phi2^2, and n the
 // global ordinal of the sample (the reference never resets the recurrence per pixel, Q17).

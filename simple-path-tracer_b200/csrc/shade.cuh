@@ -34,7 +34,7 @@ SPT_D void sphere_frame(float3 n, float3& tan, float3& bitan) { // sphere.rs:66-
 }
 
 struct TriVerts { float3 p[3], n[3], t[3], b[3]; float2 uv[3]; };
-SPT_D void load_tri(const DScene& sc, int mesh, int tri, TriVerts& tv) {
+SPT_D void load_tri(const DScene& sc, int mesh, int tri, TriVerts& tv) { // by file-order triangle id (light sampling)
   const DMesh m = sc.meshes[mesh];
   const uint32_t* ix = sc.indices + 3 * ((size_t)m.idx_base + tri);
 #pragma unroll
@@ -48,31 +48,36 @@ SPT_D float tri_area(const TriVerts& tv) { return len3(cross3(tv.p[1] - tv.p[0],
 
 // Rebuilds the Intersection the reference fills during traversal (triangle.rs:188-213, sphere.rs:63-80,
 // instance.rs:97-104) from the compact hit record — once per accepted hit instead of on every closer candidate.
+// Triangle attributes come from the pre-gathered `shade_tris` record of the hit triangle (9 x 16-byte loads).
 SPT_D void load_hit(const DScene& sc, float3 o, float3 d, const HitRec& h, HitGeom& g) {
-  const DInstance I = sc.inst[h.inst];
   const DInstanceShade S = sc.inst_shade[h.inst];
   float3 n, tan, bitan;
-  if (I.kind == 0) {
+  if (h.tri < 0) {
+    const DInstance I = sc.inst[h.inst];
     const float3 o2 = xmat_point(I.inv0, I.inv1, I.inv2, o), d2 = xmat_vec(I.inv0, I.inv1, I.inv2, d);
     const float4 cr = sc.spheres[I.root];
     n = (xpoint_at(o2, d2, h.t) - mk3(cr)) / cr.w;
     sphere_frame(n, tan, bitan);
     g.uv = sphere_uv(n);
     g.prim_pdf = 0.25f * SPT_INV_PI;
+    g.surface = I.surface;
   } else {
-    TriVerts tv; load_tri(sc, I.mesh, h.prim, tv);
+    const float4* q = sc.shade_tris + 9 * (size_t)h.tri;
+    const float4 n0 = ldg4(q), n1 = ldg4(q + 1), n2 = ldg4(q + 2), t0 = ldg4(q + 3), t1 = ldg4(q + 4), t2 = ldg4(q + 5);
+    const float4 b0 = ldg4(q + 6), b1 = ldg4(q + 7), b2 = ldg4(q + 8);
     const float v = h.u, w = h.v, u = 1.0f - v - w;
-    n = norm3(tv.n[0] * u + tv.n[1] * v + tv.n[2] * w);
-    g.uv = make_float2(tv.uv[0].x * u + tv.uv[1].x * v + tv.uv[2].x * w, tv.uv[0].y * u + tv.uv[1].y * v + tv.uv[2].y * w);
-    tan = tv.t[0] * u + tv.t[1] * v + tv.t[2] * w;
-    bitan = tv.b[0] * u + tv.b[1] * v + tv.b[2] * w;
-    g.prim_pdf = (1.0f / fmaxf(tri_area(tv), 0.001f)) / (float)sc.meshes[I.mesh].n_tris; // Q6; bvh.rs:300-302
+    n = norm3(mk3(n0) * u + mk3(n1) * v + mk3(n2) * w);
+    g.uv = make_float2(n0.w * u + n2.w * v + t1.w * w, n1.w * u + t0.w * v + t2.w * w);
+    tan = mk3(t0) * u + mk3(t1) * v + mk3(t2) * w;
+    bitan = mk3(b0) * u + mk3(b1) * v + mk3(b2) * w;
+    g.prim_pdf = b0.w; // Q6; bvh.rs:300-302
+    g.surface = sc.inst[h.inst].surface;
   }
   g.p = xpoint_at(o, d, h.t);
   g.n = norm3(mat_rows_vec(S.it0, S.it1, S.it2, n)); // Transform::transform_normal3a, transform.rs:29-31
   g.tan = mat_rows_vec(S.fwd0, S.fwd1, S.fwd2, tan);
   g.bitan = mat_rows_vec(S.fwd0, S.fwd1, S.fwd2, bitan);
-  g.inst = h.inst; g.surface = I.surface;
+  g.inst = h.inst;
   g.duvdx = g.duvdy = make_float2(0.f, 0.f);
 }
 
@@ -174,7 +179,8 @@ struct LightSample { float3 dir, L; float pdf, dist; bool delta; };
 // LightT::sample for one light.  ShapeLight: shape_light.rs:21-43 with Instance::sample (instance.rs:115-129),
 // BvhAccel::sample (bvh.rs:293-298; triangle picked in file order — a permutation of the reference's uniform pick),
 // Triangle::sample (triangle.rs:224-270, Q6) and Sphere::sample (sphere.rs:90-116, Q5).
-SPT_D void light_sample(const DScene& sc, const DLight& l, float3 pos, DrawSrc& rng, LightSample& ls) {
+template <class RNG>
+SPT_D void light_sample(const DScene& sc, const DLight& l, float3 pos, RNG& rng, LightSample& ls) {
   ls.delta = l.tag <= 2;
   switch (l.tag) {
     case 0: // directional.rs:27-29
@@ -197,10 +203,9 @@ SPT_D void light_sample(const DScene& sc, const DLight& l, float3 pos, DrawSrc& 
       const DInstance I = sc.inst[l.instance];
       const DInstanceShade S = sc.inst_shade[l.instance];
       float3 p, n, tan, bitan; float2 uv; float ppdf;
-      if (I.kind == 0) {
+      if ((I.kind & 0xff) == 0) {
         const float u0 = rng.next(), u1 = rng.next(); // Rng::uniform_on_sphere, rng.rs:56-63
-        const float phi = u0 * 2.0f * SPT_PI;
-        float sp, cp; sincosf(phi, &sp, &cp);
+        float sp, cp; sincos_2pi(u0, sp, cp);
         const float ct = 1.0f - 2.0f * u1, st = sqrtf(1.0f - ct * ct);
         n = mk3(st * cp, st * sp, ct);
         const float4 cr = sc.spheres[I.root];
@@ -250,7 +255,7 @@ SPT_D void light_sample(const DScene& sc, const DLight& l, float3 pos, DrawSrc& 
       const float rx = rng.next(), ry = rng.next();
       const float theta = ((float)y + ry) / (float)sc.env_h * SPT_PI;
       const float phi = ((float)x + rx) / (float)sc.env_w * 2.0f * SPT_PI;
-      float st, ct, sp, cp; sincosf(theta, &st, &ct); sincosf(phi, &sp, &cp);
+      float st, ct, sp, cp; sincospif(((float)y + ry) / (float)sc.env_h, &st, &ct); sincos_2pi(((float)x + rx) / (float)sc.env_w, sp, cp);
       ls.dir = mk3(st * sp, ct, st * cp);
       env_lookup(sc, theta, phi, ls.L, ls.pdf);
       ls.dist = INFINITY;
@@ -260,7 +265,8 @@ SPT_D void light_sample(const DScene& sc, const DLight& l, float3 pos, DrawSrc& 
 }
 
 // LightSamplerT::sample_light: uniform.rs:34-41 / power_is.rs:46-56
-SPT_D void sample_one_light(const DScene& sc, float3 pos, DrawSrc& rng, LightSample& ls) {
+template <class RNG>
+SPT_D void sample_one_light(const DScene& sc, float3 pos, RNG& rng, LightSample& ls) {
   int index; float pick;
   const float u = rng.next();
   if (sc.light_sampler == 0) { index = min((int)(u * (float)sc.n_lights), sc.n_lights - 1); pick = sc.num_light_inv; }

@@ -36,13 +36,14 @@ struct SptScene {
   // render-time buffers, grown on demand and reused across spt_render calls
   void* pool_mem = nullptr; size_t pool_bytes = 0; int pool_n = 0;
   long long* film = nullptr; size_t film_px = 0;
-  DevCounters* ctr = nullptr; uint32_t* sq_count = nullptr;
+  DevCounters* ctr = nullptr; uint32_t* batch_next = nullptr;
   uint32_t* tiles = nullptr; size_t tiles_cap = 0;
   float* out_mean = nullptr; uint8_t* out_rgb8 = nullptr; size_t out_px = 0;
   DevCounters* h_ctr = nullptr; // pinned
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[2] = {nullptr, nullptr};
   cudaEvent_t sev[4] = {nullptr, nullptr, nullptr, nullptr}; // per-stage timing (SPT_RENDER_TIME_STAGES)
+  int occ_ext = 0, occ_con = 0, occ_shade = 0; // resident blocks per SM of the persistent kernels (occupancy API)
 };
 
 namespace {
@@ -60,12 +61,17 @@ int upload(SptScene* s, const std::vector<T>& v, const T** dptr) {
   return SPT_OK;
 }
 
+// Grid of a persistent traversal kernel: `per_sm` resident blocks on every SM, fewer when there is little work.
+int persistent_grid(const SptContext* c, long long n_rays, int per_sm) {
+  const long long want = (n_rays + SPT_FETCH_CHUNK - 1) / SPT_FETCH_CHUNK; // one warp per chunk is enough
+  const long long blocks = (want + (SPT_BLOCK / 32) - 1) / (SPT_BLOCK / 32);
+  return (int)std::max<long long>(1, std::min<long long>(blocks, (long long)c->sm_count * per_sm));
+}
 int grid_for(const SptContext* c, long long n, int per_sm) {
   long long blocks = (n + SPT_BLOCK - 1) / SPT_BLOCK;
   return (int)std::max<long long>(1, std::min<long long>(blocks, (long long)c->sm_count * per_sm));
 }
 
-__global__ void k_begin_iter(DevCounters* ctr, uint32_t* sq_count) { ctr->live = 0; *sq_count = 0; }
 
 } // namespace
 
@@ -110,7 +116,7 @@ int32_t spt_scene_create(SptContext* ctx, const SptSceneDesc* desc, SptScene** o
     if (!h.nodes.empty()) memcpy(nodes4.data(), h.nodes.data(), h.nodes.size() * sizeof(spt::CwNode));
     UP(nodes4, nodes);
   }
-  UP(h.tris, tris); UP(h.tlas_inst, tlas_inst); UP(h.inst, inst); UP(h.inst_shade, inst_shade); UP(h.spheres, spheres);
+  UP(h.tris, tris); UP(h.shade_tris, shade_tris); UP(h.inst_mat, inst_mat); UP(h.tlas_inst, tlas_inst); UP(h.inst, inst); UP(h.inst_shade, inst_shade); UP(h.spheres, spheres);
   UP(h.meshes, meshes); UP(h.verts, verts); UP(h.indices, indices); UP(h.surfaces, surfaces); UP(h.materials, materials);
   UP(h.textures, textures); UP(h.mips, mips); UP(h.texels, texels); UP(h.mediums, mediums); UP(h.lights, lights);
   UP(h.light_prob, light_prob); UP(h.light_alias, light_alias); UP(h.inst_light, inst_light); UP(h.ss_cdf, ss_cdf);
@@ -121,13 +127,14 @@ int32_t spt_scene_create(SptContext* ctx, const SptSceneDesc* desc, SptScene** o
   d.n_lights = (int32_t)h.lights.size(); d.light_sampler = h.light_sampler; d.env_light_index = h.env_light_index;
   d.n_instances = (int32_t)h.inst.size(); d.tlas_empty = h.nodes.empty() || h.inst.empty();
   d.has_image_tex = h.has_image_tex ? 1 : 0;
+  d.mat_mask = h.mat_mask; d.has_medium = h.has_medium ? 1 : 0;
   d.num_light_inv = 1.0f / (float)h.lights.size(); // UniformLightSampler::new, uniform.rs:19
   s->cameras = h.cameras;
   d.camera = s->cameras[0];
   CU(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
   CU(cudaEventCreate(&s->ev[0])); CU(cudaEventCreate(&s->ev[1]));
   for (int i = 0; i < 4; i++) CU(cudaEventCreate(&s->sev[i]));
-  CU(cudaMalloc(&s->ctr, sizeof(DevCounters))); CU(cudaMalloc(&s->sq_count, sizeof(uint32_t)));
+  CU(cudaMalloc(&s->ctr, sizeof(DevCounters))); CU(cudaMalloc(&s->batch_next, sizeof(uint32_t)));
   CU(cudaMallocHost(&s->h_ctr, sizeof(DevCounters)));
   *out = s;
   return SPT_OK;
@@ -157,7 +164,7 @@ int32_t spt_scene_destroy(SptScene* s) {
   if (!s) return SPT_OK;
   cudaSetDevice(s->ctx->device);
   for (DevBuf& b : s->bufs) { cudaFree(b.d); cudaFreeHost(b.h); }
-  cudaFree(s->pool_mem); cudaFree(s->film); cudaFree(s->ctr); cudaFree(s->sq_count); cudaFree(s->tiles);
+  cudaFree(s->pool_mem); cudaFree(s->film); cudaFree(s->ctr); cudaFree(s->batch_next); cudaFree(s->tiles);
   cudaFree(s->out_mean); cudaFree(s->out_rgb8); cudaFreeHost(s->h_ctr);
   if (s->ev[0]) cudaEventDestroy(s->ev[0]);
   if (s->ev[1]) cudaEventDestroy(s->ev[1]);
@@ -174,17 +181,24 @@ static int32_t batch_device(SptScene* s, const SptRay* d_rays, int64_t n, void* 
   cudaStream_t st = stream_ ? (cudaStream_t)stream_ : s->stream;
   const bool count = (flags & SPT_RENDER_COUNT_TRAVERSAL) != 0;
   if (count) CU(cudaMemsetAsync(s->ctr, 0, sizeof(DevCounters), st));
-  if (n > 0) {
-    const int grid = grid_for(s->ctx, n, 16);
-    const float4* r4 = reinterpret_cast<const float4*>(d_rays);
-    if (!any) { if (count) k_trace_batch<true><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4, n, (HitIO*)d_out, s->ctr); else k_trace_batch<false><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4, n, (HitIO*)d_out, nullptr); }
-    else { if (count) k_occluded_batch<true><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4, n, (uint8_t*)d_out, s->ctr); else k_occluded_batch<false><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4, n, (uint8_t*)d_out, nullptr); }
+  uint64_t launches = 0;
+  const float4* r4 = reinterpret_cast<const float4*>(d_rays);
+  const int64_t CH = 1ll << 30; // the fetch cursor of one launch is 32-bit
+  for (int64_t off = 0; off < n; off += CH) {
+    const uint32_t m = (uint32_t)std::min<int64_t>(CH, n - off);
+    const int grid = persistent_grid(s->ctx, m, 8);
+    CU(cudaMemsetAsync(s->batch_next, 0, sizeof(uint32_t), st));
+    HitIO* ho = any ? nullptr : (HitIO*)d_out + off;
+    uint8_t* oo = any ? (uint8_t*)d_out + off : nullptr;
+    if (!any) { if (count) k_batch<false, true><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4 + 2 * off, m, ho, oo, s->batch_next, s->ctr); else k_batch<false, false><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4 + 2 * off, m, ho, oo, s->batch_next, nullptr); }
+    else { if (count) k_batch<true, true><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4 + 2 * off, m, ho, oo, s->batch_next, s->ctr); else k_batch<true, false><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4 + 2 * off, m, ho, oo, s->batch_next, nullptr); }
     CU(cudaGetLastError());
+    launches++;
   }
   if (stats) {
     memset(stats, 0, sizeof(*stats));
     if (any) stats->shadow_rays = (uint64_t)n; else stats->ext_rays = (uint64_t)n;
-    stats->kernel_launches = n > 0 ? 1 : 0;
+    stats->kernel_launches = launches;
     if (count) {
       CU(cudaMemcpyAsync(s->h_ctr, s->ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, st));
       CU(cudaStreamSynchronize(st));
@@ -226,19 +240,19 @@ __global__ void k_bxdf_batch(const DScene sc, const SptBxdfQuery* __restrict__ q
     const SptBxdfQuery Q = q[i];
     HitGeom g; g.p = mk3(0.f); g.n = mk3(0, 0, 1); g.tan = mk3(1, 0, 0); g.bitan = mk3(0, 1, 0);
     g.uv = make_float2(Q.texcoord[0], Q.texcoord[1]); g.duvdx = g.duvdy = make_float2(0.f, 0.f);
-    const Bsdf b = make_bsdf(sc, sc.materials[Q.material], texin_from(g));
+    const Bsdf b = make_bsdf<-1>(sc, sc.materials[Q.material], texin_from(g));
     DrawSrc rng; rng.state = 0; rng.list = q[i].rand; rng.idx = 0; rng.n = 8;
     const float3 wo = mk3(Q.wo[0], Q.wo[1], Q.wo[2]), wi = mk3(Q.wi[0], Q.wi[1], Q.wi[2]);
     BsdfSample s;
-    bsdf_sample(b, wo, rng, s);
+    bsdf_sample<-1>(b, wo, rng, s);
     SptBxdfResult R;
     if (s.need_probe) { rng.next(); rng.next(); rng.next(); s.lobe = -1; } // no scene in the hook: probe cannot run
     R.sample_wi[0] = s.wi.x; R.sample_wi[1] = s.wi.y; R.sample_wi[2] = s.wi.z;
     R.sample_f[0] = s.f.x; R.sample_f[1] = s.f.y; R.sample_f[2] = s.f.z;
     R.sample_pdf = s.pdf; R.sample_lobe = s.lobe; R.sample_dir = s.dir; R.n_rand_used = rng.idx;
-    const float3 f = bsdf_eval(b, wo, wi);
-    R.eval_f[0] = f.x; R.eval_f[1] = f.y; R.eval_f[2] = f.z; R.eval_pdf = bsdf_pdf(b, wo, wi);
-    R.is_delta = bsdf_is_delta(b) ? 1 : 0; R.bxdf_tag = b.tag;
+    const float3 f = bsdf_eval<-1>(b, wo, wi);
+    R.eval_f[0] = f.x; R.eval_f[1] = f.y; R.eval_f[2] = f.z; R.eval_pdf = bsdf_pdf<-1>(b, wo, wi);
+    R.is_delta = bsdf_is_delta<-1>(b) ? 1 : 0; R.bxdf_tag = b.tag;
     out[i] = R;
   }
 }
@@ -295,7 +309,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   // ---- buffers
   int pool_n = r->pool_size > 0 ? r->pool_size : (1 << 20);
   pool_n = std::max(SPT_BLOCK, (pool_n + SPT_BLOCK - 1) / SPT_BLOCK * SPT_BLOCK);
-  const size_t per_slot = 4 * sizeof(float4) + sizeof(int32_t) + sizeof(uint64_t) + 3 * sizeof(uint32_t) + 3 * sizeof(float4);
+  const size_t per_slot = 4 * sizeof(float4) + sizeof(int32_t) + sizeof(uint64_t) + 3 * sizeof(uint32_t) + 3 * sizeof(float4) + SPT_NQ * sizeof(uint32_t);
   if (s->pool_n != pool_n) {
     cudaFree(s->pool_mem); s->pool_mem = nullptr; s->pool_n = 0;
     CU(cudaMalloc(&s->pool_mem, per_slot * (size_t)pool_n));
@@ -317,9 +331,10 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
     P.pool.pixel = (uint32_t*)p; p += N * sizeof(uint32_t);
     P.pool.sample = (uint32_t*)p; p += N * sizeof(uint32_t);
     P.pool.flags = (uint32_t*)p; p += N * sizeof(uint32_t);
+    P.queue = (uint32_t*)p; p += N * SPT_NQ * sizeof(uint32_t);
     P.pool.n = pool_n;
   }
-  P.sq.count = s->sq_count; P.ctr = s->ctr; P.film = s->film;
+  P.ctr = s->ctr; P.film = s->film;
   // ---- tile ownership: tiles sorted by a hash, dealt round-robin -> interleaved, balanced to +-1 tile
   const int tiles_x = (r->width + tw - 1) / tw;
   const std::vector<uint32_t> mine = owned_tiles(r->width, r->height, tw, th, rank, world);
@@ -329,6 +344,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   P.width = r->width; P.height = r->height; P.max_depth = r->max_depth;
   P.sampler = r->sampler_kind; P.spp = spp; P.div_x = std::max(1, r->div_x); P.div_y = std::max(1, r->div_y);
   P.seed = r->seed;
+  P.sort_materials = (r->flags & SPT_RENDER_NO_SORT) ? 0 : 1;
   P.total_samples = (unsigned long long)mine.size() * (unsigned long long)(tw * th) * (unsigned long long)spp;
   DScene ds = s->ds;
   ds.camera = s->cameras[r->camera_index];
@@ -337,22 +353,56 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   CU(cudaMemsetAsync(s->film, 0, n_px * 3 * sizeof(long long), st));
   CU(cudaMemsetAsync(s->ctr, 0, sizeof(DevCounters), st));
   CU(cudaMemsetAsync(P.pool.flags, 0, (size_t)pool_n * sizeof(uint32_t), st));
+  CU(cudaMemsetAsync(P.pool.hit_inst, 0xff, (size_t)pool_n * sizeof(int32_t), st));
   CU(cudaEventRecord(s->ev[0], st));
-  const int grid = grid_for(s->ctx, pool_n, 16);
+  if (!s->occ_ext) { // resident blocks per SM of the persistent kernels, from the occupancy API (register / shared-memory limits)
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->occ_ext, k_extend<false>, SPT_BLOCK, 0));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->occ_con, k_connect<false>, SPT_BLOCK, 0));
+    s->occ_ext = std::max(1, s->occ_ext); s->occ_con = std::max(1, s->occ_con);
+  }
+  const int grid_ext = persistent_grid(s->ctx, pool_n, s->occ_ext), grid_con = persistent_grid(s->ctx, pool_n, s->occ_con);
+  const int grid_shade = grid_for(s->ctx, pool_n, 16);
+  const int grid_logic = (pool_n + SPT_LOGIC_BLOCK - 1) / SPT_LOGIC_BLOCK;
+  const int grid_gen = std::min(grid_logic, s->ctx->sm_count * 8);
   uint64_t iters = 0, launches = 0;
   const bool timed = (r->flags & SPT_RENDER_TIME_STAGES) != 0;
-  double stage[6] = {0, 0, 0, 0, 0, 0}; // generate (fused into shade), extend, shade, connect, resolve, other
+  double stage[6] = {0, 0, 0, 0, 0, 0}; // generate (inside shade), extend, shade (logic..generate), connect, resolve, other
+  const uint32_t mats = P.sort_materials ? ds.mat_mask : 0u;
+  const bool special = ds.has_medium || ds.env_tex != nullptr;
+  auto iteration = [&]() {
+    k_logic<<<grid_logic, SPT_LOGIC_BLOCK, 0, st>>>(ds, P); launches++;
+    if (special) { k_special<<<grid_shade, SPT_BLOCK, 0, st>>>(ds, P); launches++; }
+#define SHADE(M) if (mats & (1u << M)) { k_shade<M, false><<<grid_shade, SPT_BLOCK, 0, st>>>(ds, P); launches++; }
+    SHADE(0) SHADE(1) SHADE(2) SHADE(3) SHADE(4) SHADE(5) SHADE(6)
+#undef SHADE
+    if (mats & (1u << 7)) { if (count) k_shade<7, true><<<grid_shade, SPT_BLOCK, 0, st>>>(ds, P); else k_shade<7, false><<<grid_shade, SPT_BLOCK, 0, st>>>(ds, P); launches++; }
+    if (!P.sort_materials) { if (count) k_shade<-1, true><<<grid_shade, SPT_BLOCK, 0, st>>>(ds, P); else k_shade<-1, false><<<grid_shade, SPT_BLOCK, 0, st>>>(ds, P); launches++; }
+    k_generate<<<grid_gen, SPT_LOGIC_BLOCK, 0, st>>>(ds, P); launches++;
+    if (timed) cudaEventRecord(s->sev[1], st);
+    if (count) k_connect<true><<<grid_con, SPT_BLOCK, 0, st>>>(ds, P); else k_connect<false><<<grid_con, SPT_BLOCK, 0, st>>>(ds, P);
+    if (timed) cudaEventRecord(s->sev[2], st);
+    if (count) k_extend<true><<<grid_ext, SPT_BLOCK, 0, st>>>(ds, P); else k_extend<false><<<grid_ext, SPT_BLOCK, 0, st>>>(ds, P);
+    launches += 2; iters++;
+  };
   if (r->max_depth > 0 && P.total_samples > 0) {
+    // The host only needs the device counters to know when to stop.  While camera samples remain, it looks every
+    // `stride` iterations (the cursor tells how far the render is); once the cursor is exhausted the pool drains
+    // within max_depth iterations and the host looks after every one.
+    const uint64_t est_total = std::max<uint64_t>(1, P.total_samples / (uint64_t)pool_n);
     for (;;) {
-      k_begin_iter<<<1, 1, 0, st>>>(s->ctr, s->sq_count);
-      if (timed) cudaEventRecord(s->sev[0], st);
-      if (count) k_shade<true><<<grid, SPT_BLOCK, 0, st>>>(ds, P); else k_shade<false><<<grid, SPT_BLOCK, 0, st>>>(ds, P);
-      if (timed) cudaEventRecord(s->sev[1], st);
-      if (count) k_connect<true><<<grid, SPT_BLOCK, 0, st>>>(ds, P); else k_connect<false><<<grid, SPT_BLOCK, 0, st>>>(ds, P);
-      if (timed) cudaEventRecord(s->sev[2], st);
-      if (count) k_extend<true><<<grid, SPT_BLOCK, 0, st>>>(ds, P); else k_extend<false><<<grid, SPT_BLOCK, 0, st>>>(ds, P);
-      if (timed) cudaEventRecord(s->sev[3], st);
-      launches += 4; iters++;
+      int stride = 1;
+      if (!timed && iters > 0 && s->h_ctr->cursor < P.total_samples) {
+        const double done = (double)s->h_ctr->cursor / (double)P.total_samples;
+        const double per_iter = done / (double)iters;                       // fraction of the samples started per iteration
+        const double left = per_iter > 0 ? (1.0 - done) / per_iter : 1.0;   // iterations until the cursor runs out
+        stride = (int)std::max(1.0, std::min(64.0, left * 0.5));
+      }
+      (void)est_total;
+      for (int k = 0; k < stride; k++) {
+        if (timed) cudaEventRecord(s->sev[0], st);
+        iteration();
+        if (timed) cudaEventRecord(s->sev[3], st);
+      }
       CU(cudaMemcpyAsync(s->h_ctr, s->ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, st));
       CU(cudaStreamSynchronize(st));
       CU(cudaGetLastError());
@@ -361,7 +411,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
         cudaEventElapsedTime(&a, s->sev[0], s->sev[1]); cudaEventElapsedTime(&b, s->sev[1], s->sev[2]); cudaEventElapsedTime(&c, s->sev[2], s->sev[3]);
         stage[2] += a * 1e-3; stage[3] += b * 1e-3; stage[1] += c * 1e-3;
       }
-      if (s->h_ctr->live == 0) break;
+      if (s->h_ctr->it.live == 0) break;
     }
   }
   k_resolve<<<grid_for(s->ctx, (long long)n_px * 3, 8), 256, 0, st>>>(s->film, (int)n_px, 1.0f / (float)spp, d_mean, d_rgb8);

@@ -10,19 +10,32 @@
 // same un-normalised object-space ray (core/ray.rs:33-41), so `t` is comparable bit for bit; only the order in
 // which equal-t candidates are met differs.
 //
-// Traversal: one thread per ray, node groups (base index + hit bitmask) on a short per-thread stack, children
-// visited in octant order, 5 x 16-byte loads per node, 3 x 16-byte loads per triangle, 4 per instance.
+// Traversal: one thread per ray, node groups (base index + hit bitmask) on a short per-thread stack kept in SHARED
+// memory (overflow in local memory), children visited in octant order, 5 x 16-byte loads per node, 3 x 16-byte
+// loads per triangle, 4 per instance.  Warps are PERSISTENT: a lane whose ray is finished pulls the next ray from a
+// warp-private chunk of the launch's ray range (one global atomic per 256 rays), so short and long rays do not
+// leave lanes idle; all lanes of a warp advance in rounds of exactly one node step followed by the leaf work that
+// node produced (triangles / instances), which keeps the 200-instruction node step converged across the warp.
 #pragma once
 #include "scene.h"
 #include "vecmath.cuh"
 
 struct HitRec {
   float t, u, v;
-  int prim, inst;
+  int prim, inst; // prim: triangle id inside its mesh (file order) or 0 for a sphere; inst: instance id, -1 = miss
+  int tri;        // global index of the triangle in `tris` / `shade_tris` (leaf order), -1 for a sphere
 };
 struct TravCounters { uint32_t nodes, tris, insts; };
 
-#define SPT_STACK 32
+#define SPT_TRAV_BLOCK 128  // threads per block of every traversal kernel
+#define SPT_SSTACK 16       // stack entries per thread in shared memory
+#define SPT_LSTACK 32       // overflow entries in local memory (untouched unless a ray goes deeper than SPT_SSTACK)
+#ifndef SPT_FETCH_CHUNK
+#define SPT_FETCH_CHUNK 256 // rays a warp reserves per global atomic
+#endif
+#ifndef SPT_FETCH_MIN_IDLE
+#define SPT_FETCH_MIN_IDLE 6 // refill the warp once this many lanes are without a ray
+#endif
 
 SPT_D uint32_t sext_s8x4(uint32_t x) { uint32_t v; asm("prmt.b32 %0, %1, 0x0, 0x0000BA98;" : "=r"(v) : "r"(x)); return v; }
 SPT_D uint32_t bfind_u32(uint32_t x) { uint32_t v; asm("bfind.u32 %0, %1;" : "=r"(v) : "r"(x)); return v; }
@@ -125,79 +138,158 @@ SPT_D bool sphere_roots(float4 cr, float3 o, float3 d, float& mn, float& mx) {
   return false;
 }
 
-// ANY = false: closest hit in (tmin, hit.t) -> fills hit, returns whether something was hit.
-// ANY = true : returns true as soon as any primitive is hit in (tmin, tmax = hit.t).
-template <bool ANY, bool COUNT>
-__device__ bool traverse(const DScene& sc, float3 ow, float3 dw, float tmin, HitRec& hit, TravCounters* cnt) {
-  if (sc.tlas_empty) return false;
-  uint2 stack[SPT_STACK];
-  int sp = 0, blas_base = 0, cur_inst = -1;
-  bool found = false;
+// ---- per-ray traversal state (registers) + the two-level stack ------------------------------------------------------
+struct TravStack {
+  uint2* sh;     // &s_stack[0][threadIdx.x]; entry i at sh[i * SPT_TRAV_BLOCK]
+  uint2* lo;     // local-memory overflow
+  SPT_D void push(int& sp, uint2 e) const { if (sp < SPT_SSTACK) sh[sp * SPT_TRAV_BLOCK] = e; else lo[sp - SPT_SSTACK] = e; sp++; }
+  SPT_D uint2 pop(int& sp) const { --sp; return sp < SPT_SSTACK ? sh[sp * SPT_TRAV_BLOCK] : lo[sp - SPT_SSTACK]; }
+};
+struct Trav {
+  float3 ow, dw; // the world-space ray (core/ray.rs); r holds the ray of the current space (world or object)
+  float tmin;
   RaySetup r;
-  ray_setup(r, ow, dw);
-  uint2 ng = make_uint2(0u, 0x80000000u), tg = make_uint2(0u, 0u);
+  HitRec hit;    // hit.t doubles as the running t_max (Intersection::t, intersection.rs:21-26)
+  uint2 ng, tg;  // current node group / primitive group
+  int sp, blas_base, cur_inst;
+};
+SPT_D void trav_begin(Trav& T, float3 o, float3 d, float tmin, float tmax) {
+  T.ow = o; T.dw = d; T.tmin = tmin;
+  ray_setup(T.r, o, d);
+  T.hit.t = tmax; T.hit.u = T.hit.v = 0.f; T.hit.prim = -1; T.hit.inst = -1; T.hit.tri = -1; // Intersection::default
+  T.ng = make_uint2(0u, 0x80000000u); T.tg = make_uint2(0u, 0u);
+  T.sp = 0; T.blas_base = 0; T.cur_inst = -1;
+}
+
+// One round: exactly one node step (T.ng holds at least one pending child on entry), then all the leaf work up to
+// the next node step.  Returns true when the ray is finished (ANY: also when an occluder was found, hit.inst = 0).
+// ANY = false: closest hit in (tmin, hit.t) -> hit.  ANY = true: any primitive in (tmin, tmax = hit.t).
+template <bool ANY, bool COUNT>
+SPT_D bool trav_round(const DScene& sc, Trav& T, const TravStack& st, TravCounters& cnt) {
+  {
+    const uint32_t bit = bfind_u32(T.ng.y);
+    const uint32_t base = T.ng.x, imask = T.ng.y;
+    T.ng.y &= ~(1u << bit);
+    if (T.ng.y > 0x00ffffffu) st.push(T.sp, T.ng);
+    const uint32_t slot = (bit - 24u) ^ (T.r.octinv4 & 0xffu);
+    const uint32_t rel = __popc(imask & ~(0xffffffffu << slot));
+    if (COUNT) cnt.nodes++;
+    node_children(sc.nodes, base + rel, T.r, T.tmin, T.hit.t, T.ng, T.tg);
+  }
   for (;;) {
-    if (ng.y > 0x00ffffffu) {
-      const uint32_t bit = bfind_u32(ng.y);
-      const uint32_t base = ng.x, imask = ng.y;
-      ng.y &= ~(1u << bit);
-      if (ng.y > 0x00ffffffu) stack[sp++] = ng;
-      const uint32_t slot = (bit - 24u) ^ (r.octinv4 & 0xffu);
-      const uint32_t rel = __popc(imask & ~(0xffffffffu << slot));
-      if (COUNT) cnt->nodes++;
-      node_children(sc.nodes, base + rel, r, tmin, hit.t, ng, tg);
-    } else {
-      tg = ng;
-      ng = make_uint2(0u, 0u);
-    }
-    while (tg.y != 0u) {
-      const uint32_t k = bfind_u32(tg.y);
-      tg.y &= ~(1u << k);
-      const uint32_t pidx = tg.x + k;
-      if (cur_inst < 0) { // TLAS leaf: an instance (instance.rs:89-109)
+    while (T.tg.y != 0u) {
+      const uint32_t k = bfind_u32(T.tg.y);
+      T.tg.y &= ~(1u << k);
+      const uint32_t pidx = T.tg.x + k;
+      if (T.cur_inst < 0) { // TLAS leaf: an instance (instance.rs:89-109)
         const int iid = sc.tlas_inst[pidx];
         const float4* ip = reinterpret_cast<const float4*>(sc.inst + iid);
         const float4 r0 = ldg4(ip), r1 = ldg4(ip + 1), r2 = ldg4(ip + 2), mt = ldg4(ip + 3);
-        if (COUNT) cnt->insts++;
-        const float3 o2 = xmat_point(r0, r1, r2, ow), d2 = xmat_vec(r0, r1, r2, dw);
+        if (COUNT) cnt.insts++;
+        const float3 o2 = xmat_point(r0, r1, r2, T.ow), d2 = xmat_vec(r0, r1, r2, T.dw);
         const int kind = __float_as_int(mt.x), root = __float_as_int(mt.y);
         if (kind == 0) { // sphere
-          if (COUNT) cnt->tris++;
+          if (COUNT) cnt.tris++;
           float mn, mx;
           if (sphere_roots(ldg4(sc.spheres + root), o2, d2, mn, mx)) {
-            if (ANY) { if (mn < hit.t && mx > tmin) return true; } // sphere.rs:51-57
+            if (ANY) { if (mn < T.hit.t && mx > T.tmin) { T.hit.inst = 0; return true; } } // sphere.rs:51-57
             else {
-              const float t = mn < tmin ? mx : mn;                 // sphere.rs:59-63
-              if (tmin < t && t < hit.t) { hit.t = t; hit.u = 0.f; hit.v = 0.f; hit.prim = 0; hit.inst = iid; found = true; }
+              const float t = mn < T.tmin ? mx : mn;                                      // sphere.rs:59-63
+              if (T.tmin < t && t < T.hit.t) { T.hit.t = t; T.hit.u = 0.f; T.hit.v = 0.f; T.hit.prim = 0; T.hit.tri = -1; T.hit.inst = iid; }
+            }
+          }
+        } else if (kind & 2) { // small mesh: its few triangles directly, same object-space ray as the BLAS would see
+          const int n = kind >> 8;
+          for (int j = 0; j < n; j++) {
+            if (COUNT) cnt.tris++;
+            float t, v, w; int tid;
+            if (tri_test(sc.tris, (uint32_t)(root + j), o2, d2, t, v, w, tid) && t > T.tmin && t < T.hit.t) {
+              if (ANY) { T.hit.inst = 0; return true; }
+              T.hit.t = t; T.hit.u = v; T.hit.v = w; T.hit.prim = tid; T.hit.tri = root + j; T.hit.inst = iid;
             }
           }
         } else { // enter the BLAS with the object-space ray
-          if (tg.y != 0u) stack[sp++] = tg;
-          if (ng.y > 0x00ffffffu) stack[sp++] = ng;
-          blas_base = sp; cur_inst = iid;
-          ray_setup(r, o2, d2);
-          ng = make_uint2((uint32_t)root, 0x80000000u);
-          tg = make_uint2(0u, 0u);
-          break;
+          if (T.tg.y != 0u) st.push(T.sp, T.tg);
+          if (T.ng.y > 0x00ffffffu) st.push(T.sp, T.ng);
+          T.blas_base = T.sp; T.cur_inst = iid;
+          ray_setup(T.r, o2, d2);
+          T.ng = make_uint2((uint32_t)root, 0x80000000u);
+          T.tg = make_uint2(0u, 0u);
+          return false;
         }
       } else {
-        if (COUNT) cnt->tris++;
+        if (COUNT) cnt.tris++;
         float t, v, w; int tid;
-        if (tri_test(sc.tris, pidx, r.o, r.d, t, v, w, tid)) {
-          if (t > tmin && t < hit.t) { // triangle.rs:177-187
-            if (ANY) return true;
-            hit.t = t; hit.u = v; hit.v = w; hit.prim = tid; hit.inst = cur_inst; found = true;
+        if (tri_test(sc.tris, pidx, T.r.o, T.r.d, t, v, w, tid)) {
+          if (t > T.tmin && t < T.hit.t) { // triangle.rs:177-187
+            if (ANY) { T.hit.inst = 0; return true; }
+            T.hit.t = t; T.hit.u = v; T.hit.v = w; T.hit.prim = tid; T.hit.tri = (int)pidx; T.hit.inst = T.cur_inst;
           }
         }
       }
     }
-    if (ng.y <= 0x00ffffffu) {
-      if (cur_inst >= 0 && sp == blas_base) { cur_inst = -1; ray_setup(r, ow, dw); }
-      if (sp == 0) break;
-      ng = stack[--sp];
-    }
+    if (T.ng.y > 0x00ffffffu) return false;
+    if (T.cur_inst >= 0 && T.sp == T.blas_base) { T.cur_inst = -1; ray_setup(T.r, T.ow, T.dw); }
+    if (T.sp == 0) return true;
+    T.ng = st.pop(T.sp);
+    if (T.ng.y > 0x00ffffffu) return false;
+    T.tg = T.ng; T.ng = make_uint2(0u, 0u); // a postponed primitive group: test it now, the next round starts at a node
   }
-  return found;
+}
+
+// Single-ray query (used inside shading for the BSSRDF probe): runs the rounds back to back.
+template <bool ANY, bool COUNT>
+SPT_D bool traverse(const DScene& sc, float3 ow, float3 dw, float tmin, HitRec& hit, TravCounters& cnt, const TravStack& st) {
+  if (sc.tlas_empty) return false;
+  Trav T;
+  trav_begin(T, ow, dw, tmin, hit.t);
+  while (!trav_round<ANY, COUNT>(sc, T, st, cnt)) {}
+  hit = T.hit;
+  return hit.inst >= 0;
+}
+
+// Persistent-warp driver.  Src provides
+//   uint32_t total() const;                                            number of candidate rays of this launch
+//   bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax);   false: nothing to trace at i
+//   void store(uint32_t i, const HitRec& h);                           closest hit (inst = -1: miss) / ANY: inst = 0 occluded
+// `next` is a zero-initialised device counter of this launch.  Must be called by all threads of a block of
+// SPT_TRAV_BLOCK threads (uses a static shared-memory stack).
+template <bool ANY, bool COUNT, class Src>
+SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCounters& cnt) {
+  __shared__ uint2 s_stack[SPT_SSTACK][SPT_TRAV_BLOCK];
+  uint2 l_stack[SPT_LSTACK];
+  TravStack st; st.sh = &s_stack[0][threadIdx.x]; st.lo = l_stack;
+  const uint32_t total = src.total(), lane = threadIdx.x & 31u, FULL = 0xffffffffu;
+  uint32_t w_next = 0, w_end = 0, idx = 0;
+  bool exhausted = false, has = false;
+  Trav T;
+  for (;;) {
+    const uint32_t idle = __ballot_sync(FULL, !has);
+    if (idle == FULL || __popc(idle) >= SPT_FETCH_MIN_IDLE) {
+      if (w_next >= w_end && !exhausted) { // reserve the next chunk for this warp
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(next, (uint32_t)SPT_FETCH_CHUNK);
+        base = __shfl_sync(FULL, base, 0);
+        if (base >= total) exhausted = true;
+        else { w_next = base; w_end = min(base + (uint32_t)SPT_FETCH_CHUNK, total); }
+      }
+      const uint32_t avail = w_end - w_next; // w_end >= w_next always
+      const uint32_t take = min((uint32_t)__popc(idle), avail);
+      if (take == 0 && idle == FULL) break;  // nothing in flight and nothing left (exhausted)
+      const uint32_t rank = __popc(idle & ((1u << lane) - 1u));
+      if (!has && rank < take) {
+        idx = w_next + rank;
+        float3 o, d; float tmin, tmax;
+        has = src.load(idx, o, d, tmin, tmax);
+        if (has) {
+          if (sc.tlas_empty) { HitRec h; h.t = tmax; h.u = h.v = 0.f; h.prim = h.inst = h.tri = -1; src.store(idx, h); has = false; }
+          else trav_begin(T, o, d, tmin, tmax);
+        }
+      }
+      w_next += take;
+    }
+    if (has && trav_round<ANY, COUNT>(sc, T, st, cnt)) { src.store(idx, T.hit); has = false; }
+  }
 }
 
 // sphere_normal_to_texcoords (sphere.rs:138-145)

@@ -43,6 +43,9 @@ SPT_HD float clampf_(float x, float lo, float hi) { return x < lo ? lo : (x > hi
 SPT_HD float sqr(float x) { return x * x; }
 
 #ifdef __CUDACC__
+// sin/cos of 2*pi*u for u in [0,1]: sincospif has an exact, branch-free range reduction (no Payne-Hanek slow path,
+// which sincosf would inline at every call site).
+SPT_D void sincos_2pi(float u, float& s, float& c) { sincospif(2.0f * u, &s, &c); }
 // ---- exact (non-contracted) arithmetic for the geometric leaf tests --------------------------------------
 SPT_D float xmul(float a, float b) { return __fmul_rn(a, b); }
 SPT_D float xadd(float a, float b) { return __fadd_rn(a, b); }

@@ -1,21 +1,30 @@
-// wavefront.cuh — the wavefront path-tracing kernels (generate / extend / shade / connect / resolve).
+// wavefront.cuh — shared definitions of the wavefront path-tracing kernels (kernels.cuh).
 //
 // Replaces PathTracer::render + trace_ray (src/renderer/pt.rs:39-295): instead of one recursive loop per pixel
-// sample, a pool of resident paths (SoA in HBM/L2) is advanced one bounce per iteration:
-//     shade   : consume the hit of every live path (medium event | miss | surface), accumulate emission, sample
-//               the BxDF, emit one shadow ray (NEE) into a compacted queue, Russian roulette; a path that ends
-//               is REGENERATED in place from a global sample cursor, so the pool stays full until the image is done
-//     connect : any-hit test of the queued shadow rays, unoccluded contributions go to the film
-//     extend  : closest-hit traversal of every live path's ray
+// sample, a pool of resident paths (SoA in HBM/L2) is advanced one bounce per iteration by a chain of kernels:
+//     logic    : classify every live path by what its hit needs next -> per-class queues of slot ids
+//                (8 material classes binned by material tag, + "special" = inside a medium / environment miss)
+//     special  : medium events (Homogeneous::sample_pi/sample_wi, NEE from inside the medium) and environment hits
+//     shade<M> : one kernel per material class present in the scene: rebuild the hit, emission + MIS, BxDF sample,
+//                NEE shadow ray into a compacted queue, Russian roulette.  Binning removes the 8-way BxDF divergence
+//                and lets each class compile to its own register budget.
+//     generate : finished slots are REGENERATED in place from a global camera-sample cursor (pixel sampler + camera),
+//                so the pool stays full until the image is done
+//     connect  : any-hit test of the queued shadow rays, unoccluded contributions go to the film
+//     extend   : closest-hit traversal of every live path's ray
 // Film: 64-bit fixed-point sums (2^-24) updated with integer atomics, so the image is independent of the order
 // in which paths finish — bit-identical across pool sizes, tile ownership and GPU counts.
 #pragma once
 #include "shade.cuh"
 
+#define SPT_NQ 10        // shade queues: 0..7 = material tag, 8 = special (medium / environment), 9 = unsorted surfaces
+#define SPT_Q_SPECIAL 8
+#define SPT_Q_GENERIC 9
+
 struct PathPool { // SoA over `n` slots
   float4* ray_o;    // origin.xyz, t_min
   float4* ray_d;    // direction.xyz, -
-  float4* hit;      // t, u, v, prim (int bits)
+  float4* hit;      // t, u, v, global triangle index (int bits; -1 = sphere)
   int32_t* hit_inst;
   float4* thr;      // throughput.rgb, last_sample_pdf
   uint64_t* rng;
@@ -24,22 +33,31 @@ struct PathPool { // SoA over `n` slots
   uint32_t* flags;  // bit0 alive | depth << 8 | (medium+1) << 16
   int32_t n;
 };
-struct ShadowQueue { float4* o; float4* d; float4* c; uint32_t* count; }; // o.xyz,tmin | d.xyz,tmax | contrib.rgb,pixel
+struct ShadowQueue { float4* o; float4* d; float4* c; }; // o.xyz,tmin | d.xyz,tmax | contrib.rgb,pixel
+struct IterCounters { // per-iteration device counters; each is zeroed by a kernel that runs between its consumer and its next producer
+  uint32_t q[SPT_NQ];   // shade-queue fill      (producer: logic/special, consumers: special/shade, zeroed by generate)
+  uint32_t sq;          // shadow-queue fill     (producer: special/shade, consumer: connect, zeroed by extend)
+  uint32_t live;        // live slots after generate (read by the host; zeroed by logic)
+  uint32_t next_ext;    // ray-fetch cursor of extend  (zeroed by logic)
+  uint32_t next_con;    // ray-fetch cursor of connect (zeroed by extend)
+  uint32_t pad[2];
+};
 struct DevCounters { // device-side totals of one render
   unsigned long long cursor;      // next camera-sample ordinal
   unsigned long long paths, ext_rays, shadow_rays, probe_rays, nonfinite, nodes, tris, insts;
-  uint32_t live;                  // live slots after the last shade pass
-  uint32_t pad;
+  IterCounters it;
 };
 struct RenderParams {
   PathPool pool;
   ShadowQueue sq;
+  uint32_t* queue;   // SPT_NQ arrays of pool.n slot ids
   DevCounters* ctr;
   long long* film; // 3 per pixel
   const uint32_t* tiles; // owned tile ids
   int32_t n_tiles, tiles_x, tile_w, tile_h;
   int32_t width, height, max_depth;
   int32_t sampler, spp, div_x, div_y;
+  int32_t sort_materials; // 0: every surface hit goes to the generic queue (SPT_RENDER_NO_SORT)
   uint64_t seed;
   unsigned long long total_samples; // n_tiles * tile_w * tile_h * spp
 };
@@ -96,7 +114,8 @@ SPT_D bool ordinal_to_sample(const RenderParams& P, unsigned long long s, uint32
 }
 
 // PixelSamplerT::next_sample in closed form (recurrence.rs:41-56, random.rs:31-38, jittered.rs:44-57 with Q16 fixed)
-SPT_D void pixel_offset(const RenderParams& P, uint32_t pixel, uint32_t k, DrawSrc& rng, float& ox, float& oy) {
+template <class RNG>
+SPT_D void pixel_offset(const RenderParams& P, uint32_t pixel, uint32_t k, RNG& rng, float& ox, float& oy) {
   if (P.sampler == 2) r2_offset((uint32_t)((unsigned long long)pixel * (unsigned long long)P.spp + k) + 1u, ox, oy);
   else if (P.sampler == 0) { ox = rng.next(); oy = rng.next(); }
   else {
@@ -119,19 +138,17 @@ SPT_D void film_xy(const RenderParams& P, uint32_t pixel, float ox, float oy, fl
 
 // Intersect ONE leaf primitive with a ray — BasicPrimitiveRef::intersect as used by shadow_ray_from_medium
 // (pt.rs:212-233).  The reference passes the WORLD-space ray to the object-space primitive; reproduced.
-SPT_D bool leaf_intersect(const DScene& sc, int inst, int prim, float3 o, float3 d, float tmin, float tmax, float& t_out) {
+SPT_D bool leaf_intersect(const DScene& sc, int inst, int tri, float3 o, float3 d, float tmin, float tmax, float& t_out) {
   const DInstance I = sc.inst[inst];
-  if (I.kind == 0) {
+  if (tri < 0) {
     float mn, mx;
     if (!sphere_roots(sc.spheres[I.root], o, d, mn, mx)) return false;
     const float t = mn < tmin ? mx : mn;
     if (tmin < t && t < tmax) { t_out = t; return true; }
     return false;
   }
-  const DMesh m = sc.meshes[I.mesh];
-  const uint32_t* ix = sc.indices + 3 * ((size_t)m.idx_base + prim);
-  const float3 p0 = mk3(sc.verts[4 * ((size_t)m.vert_base + ix[0])]), p1 = mk3(sc.verts[4 * ((size_t)m.vert_base + ix[1])]),
-               p2 = mk3(sc.verts[4 * ((size_t)m.vert_base + ix[2])]);
+  const float4* tp = sc.tris + 3 * (size_t)tri;
+  const float3 p0 = mk3(ldg4(tp)), p1 = mk3(ldg4(tp + 1)), p2 = mk3(ldg4(tp + 2));
   const float3 e1 = xsub3(p1, p0), e2 = xsub3(p2, p0), q = xcross3(d, e2);
   float det = xdot3(e1, q);
   if (det == 0.0f) return false;
