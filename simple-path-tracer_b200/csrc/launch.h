@@ -1,0 +1,34 @@
+// launch.h — host-callable launchers of the device kernels.  Each group of kernels lives in its own translation unit
+// (trav_kernels.cu, shade_*.cu, misc_kernels.cu) so they compile in parallel; spt_api.cu holds only host code.
+#pragma once
+#include <cuda_runtime.h>
+#include "../../include/spt.h"
+#include "scene.h"
+#include "wavefront_types.h"
+
+#define SPT_TRAV_BLOCK 128  // threads per block of every traversal / shade kernel
+#define SPT_LOGIC_BLOCK 256
+#ifndef SPT_FETCH_CHUNK
+#define SPT_FETCH_CHUNK 32  // rays a warp reserves at a time
+#endif
+
+struct HitIO { float t, u, v; int prim, inst; };
+
+namespace spt {
+// resident blocks per SM (occupancy API) of the persistent traversal kernels
+cudaError_t occupancy_traversal(int* extend_blocks, int* connect_blocks, int* batch_blocks);
+void launch_extend(const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st);
+void launch_connect(const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st);
+void launch_batch(const DScene& sc, const float4* rays, uint32_t n, HitIO* hits, uint8_t* occ, uint32_t* next, DevCounters* ctr,
+                  bool any, bool count, int grid, cudaStream_t st);
+void launch_logic(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st);
+void launch_special(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st);
+void launch_shade(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st); // mat = -1: unsorted
+void launch_generate(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st);
+void launch_resolve(const long long* film, int n_pixels, float inv_spp, float* out_mean, uint8_t* out_rgb8, int grid, cudaStream_t st);
+void launch_bxdf(const DScene& sc, const SptBxdfQuery* q, long long n, SptBxdfResult* out, int grid, cudaStream_t st);
+// defined per shade translation unit
+void launch_shade_a(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st); // 0..3
+void launch_shade_b(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st); // 4..6
+void launch_shade_c(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st); // 7, -1
+} // namespace spt

@@ -1,0 +1,202 @@
+// misc_kernels.cu — logic (binning), special (media / environment), generate (camera + pixel sampler), resolve (film) and
+// the BxDF test-hook kernel.
+#include "launch.h"
+#include "shade_kernels.cuh"
+
+// ---- logic: bin the live paths by the kind of work their hit needs ---------------------------------------------------
+// Dense pass in slot order, one slot per thread; queue space is reserved with ONE global atomic per class per block
+// (shared-memory counters inside the block), so the queues stay nearly slot-ordered and the shade kernels' gathers
+// stay mostly coalesced.
+__global__ void __launch_bounds__(SPT_LOGIC_BLOCK) k_logic(const DScene sc, const RenderParams P) {
+  __shared__ uint32_t s_cnt[SPT_NQ], s_base[SPT_NQ];
+  if (threadIdx.x < SPT_NQ) s_cnt[threadIdx.x] = 0;
+  if (blockIdx.x == 0 && threadIdx.x == 0) { P.ctr->it.live = 0; P.ctr->it.next_ext = 0; }
+  __syncthreads();
+  const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+  int cls = -1; uint32_t rank = 0;
+  if (slot < P.pool.n) {
+    const uint32_t flags = P.pool.flags[slot];
+    if (flags & 1u) {
+      const int inst = P.pool.hit_inst[slot];
+      if ((flags >> 16) != 0u) cls = SPT_Q_SPECIAL;                       // inside a medium (pt.rs:56-96)
+      else if (inst < 0) { if (sc.env_tex) cls = SPT_Q_SPECIAL; else P.pool.flags[slot] = 0u; } // miss (pt.rs:97-111)
+      else cls = P.sort_materials ? (int)sc.inst_mat[inst] : SPT_Q_GENERIC; // surface hit (pt.rs:112-193)
+    }
+    if (cls >= 0) rank = atomicAdd(&s_cnt[cls], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x < SPT_NQ && s_cnt[threadIdx.x]) s_base[threadIdx.x] = atomicAdd(&P.ctr->it.q[threadIdx.x], s_cnt[threadIdx.x]);
+  __syncthreads();
+  if (cls >= 0) P.queue[(size_t)cls * P.pool.n + s_base[cls] + rank] = (uint32_t)slot;
+}
+
+// ---- special: paths inside a medium (pt.rs:56-96) and environment hits (pt.rs:97-111) -----------------------------------------
+// A path that leaves its medium is handed on to the material queue of the surface it left through, to be shaded in
+// this same iteration with the cached hit (Q21: the reference re-traces the same ray and finds the same hit).
+__global__ void __launch_bounds__(SPT_BLOCK) k_special(const DScene sc, const RenderParams P) {
+  uint32_t nonfinite = 0;
+  const uint32_t n = P.ctr->it.q[SPT_Q_SPECIAL];
+  const uint32_t* queue = P.queue + (size_t)SPT_Q_SPECIAL * P.pool.n;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int slot = (int)queue[i];
+    const uint32_t flags = P.pool.flags[slot];
+    PathRegs s; HitRec hit;
+    load_path(P, slot, flags, s, hit);
+    const bool does_hit = hit.inst >= 0;
+    ShadowRay sh; sh.emit = false; sh.o = sh.d = sh.c = mk3(0.f); sh.tmin = sh.tmax = 0.f;
+    bool terminate = false, scattered = false;
+    if (s.medium >= 0) {
+      const DMedium md = sc.mediums[s.medium];
+      const float3 sig_t = mk3(md.sigma_t[0], md.sigma_t[1], md.sigma_t[2]), sig_s = mk3(md.sigma_s[0], md.sigma_s[1], md.sigma_s[2]);
+      const float3 wo = -s.rd;
+      // Homogeneous::sample_pi, homogeneous.rs:31-60
+      const float rx = s.rng.next(), ry = s.rng.next();
+      const float sst = rx < 1.0f / 3.0f ? sig_t.x : (rx < 2.0f / 3.0f ? sig_t.y : sig_t.z);
+      const float sample_t = -logf(1.0f - ry) / sst;
+      const float tm = fminf(sample_t, hit.t);
+      const float3 att = exp3(-sig_t * tm);
+      const float3 pi = s.ro - wo * tm;
+      if (sample_t < hit.t) {
+        s.thr *= att * sig_s / avg3(sig_t * att);
+        scattered = true;
+        if (!does_hit) terminate = true; // the reference panics here (pt.rs:77 unwrap on None)
+        else {
+          if (sc.n_lights > 0) {
+            LightSample ls;
+            sample_one_light(sc, pi, s.rng, ls);
+            const float phase = hg_phase(md.g, dot3(wo, ls.dir));
+            // shadow_ray_from_medium, pt.rs:212-233
+            float tl, transported, tmin_s = 1e-4f;
+            if (leaf_intersect(sc, hit.inst, hit.tri, pi, ls.dir, 1e-4f, ls.dist - 0.001f, tl)) { transported = tl; tmin_s += tl; }
+            else { transported = ls.dist; tmin_s += ls.dist - 0.001f; }
+            const float3 atten = exp3(-sig_t * transported);
+            if (ls.pdf != 0.0f && isfinite(ls.pdf)) {
+              const float3 li = ls.delta ? atten * phase * ls.L / ls.pdf : atten * phase * ls.L * power_heuristic(ls.pdf, phase) / ls.pdf;
+              sh.emit = true; sh.o = pi; sh.d = ls.dir; sh.tmin = tmin_s; sh.tmax = ls.dist - 0.001f; sh.c = s.thr * li;
+            }
+          }
+          // Homogeneous::sample_wi, homogeneous.rs:62-71
+          const float u0 = s.rng.next(), u1 = s.rng.next();
+          const float ct = hg_cdf_inverse(md.g, u0), st = sqrtf(1.0f - ct * ct);
+          float sp, cp; sincos_2pi(u1, sp, cp);
+          s.rd = medium_local_to_world(wo, mk3(st * cp, st * sp, ct));
+          s.last_pdf = hg_phase(md.g, ct);
+          s.ro = pi; s.rtmin = 1e-4f;
+        }
+      } else { // left the medium
+        s.thr *= att / avg3(att);
+        s.medium = -1;
+      }
+    }
+    bool to_surface = false;
+    if (!scattered) {
+      if (!does_hit) { // pt.rs:97-111
+        if (sc.env_tex) {
+          float3 env; float env_pdf;
+          env_eval_dir(sc, s.rd, env, env_pdf);
+          const float w = s.depth == 0 ? 1.0f : power_heuristic(s.last_pdf, pdf_env_light(sc) * env_pdf);
+          film_add(P, s.pixel, s.thr * env * w, nonfinite);
+        }
+        terminate = true;
+      } else to_surface = true;
+    }
+    push_shadow(P, sh, s.pixel);
+    if (to_surface) { // write back what the medium changed, then queue for surface shading
+      P.pool.thr[slot] = make_float4(s.thr.x, s.thr.y, s.thr.z, s.last_pdf);
+      P.pool.rng[slot] = s.rng.state;
+      P.pool.flags[slot] = 1u | ((uint32_t)s.depth << 8);
+      const int cls = P.sort_materials ? (int)sc.inst_mat[hit.inst] : SPT_Q_GENERIC;
+      const uint32_t qi = atomicAdd(&P.ctr->it.q[cls], 1u);
+      P.queue[(size_t)cls * P.pool.n + qi] = (uint32_t)slot;
+    } else finish_bounce(P, slot, s, terminate);
+  }
+  warp_sum_to(&P.ctr->nonfinite, nonfinite);
+}
+
+// ---- generate: refill finished / empty slots from the sample cursor (render loop pt.rs:263-280 + pixel sampler + camera) ----
+__global__ void __launch_bounds__(SPT_LOGIC_BLOCK) k_generate(const DScene sc, const RenderParams P) {
+  if (blockIdx.x == 0 && threadIdx.x < SPT_NQ) P.ctr->it.q[threadIdx.x] = 0; // the shade kernels of this iteration are done
+  uint32_t n_new = 0, n_live = 0;
+  for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < P.pool.n; slot += gridDim.x * blockDim.x) {
+    if (P.pool.flags[slot] & 1u) { n_live++; continue; }
+    bool got = false;
+    uint32_t k = 0, pixel = 0;
+    unsigned long long s = warp_reserve<unsigned long long>(&P.ctr->cursor, true);
+    for (;;) {
+      if (s >= P.total_samples) break;
+      if (ordinal_to_sample(P, s, pixel, k)) { got = true; break; }
+      s = atomicAdd(&P.ctr->cursor, 1ull);
+    }
+    if (!got) continue;
+    PathRng rng; rng.state = rng_init(P.seed, pixel, k);
+    float ox, oy, x, y;
+    pixel_offset(P, pixel, k, rng, ox, oy);
+    film_xy(P, pixel, ox, oy, x, y);
+    const float3 rd = camera_dir(sc.camera, x, y);
+    P.pool.ray_o[slot] = make_float4(sc.camera.eye[0], sc.camera.eye[1], sc.camera.eye[2], 1e-4f);
+    P.pool.ray_d[slot] = make_float4(rd.x, rd.y, rd.z, 0.f);
+    P.pool.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+    P.pool.rng[slot] = rng.state;
+    P.pool.pixel[slot] = pixel;
+    P.pool.sample[slot] = k;
+    P.pool.flags[slot] = 1u;
+    n_new++; n_live++;
+  }
+  warp_sum_to(&P.ctr->paths, n_new);
+  {
+    const unsigned active = __activemask();
+    const uint32_t s = __reduce_add_sync(active, n_live);
+    if (s && lane_id() == (uint32_t)(__ffs(active) - 1)) atomicAdd(&P.ctr->it.live, s);
+  }
+}
+
+// ---- resolve: Film::filter_pixel for box r<=0.5 (own-pixel mean, film.rs:68-91) + color_to_rgb (film.rs:94-99) -----
+__global__ void k_resolve(const long long* __restrict__ film, int n_pixels, float inv_spp, float* __restrict__ out_mean, uint8_t* __restrict__ out_rgb8) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 3 * n_pixels; i += gridDim.x * blockDim.x) {
+    const float sum = (float)((double)film[i] * (1.0 / 16777216.0));
+    const float m = sum * inv_spp;
+    out_mean[i] = m;
+    if (out_rgb8) out_rgb8[i] = (uint8_t)clampf_(m * 255.0f, 0.0f, 255.0f);
+  }
+}
+
+
+// ---- BxDF test hook = BxdfT::{sample,pdf,bxdf,is_delta} with caller-supplied random numbers -----------------------------------
+__global__ void k_bxdf_batch(const DScene sc, const SptBxdfQuery* __restrict__ q, long long n, SptBxdfResult* __restrict__ out) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const SptBxdfQuery Q = q[i];
+    HitGeom g; g.p = mk3(0.f); g.n = mk3(0, 0, 1); g.tan = mk3(1, 0, 0); g.bitan = mk3(0, 1, 0);
+    g.uv = make_float2(Q.texcoord[0], Q.texcoord[1]); g.duvdx = g.duvdy = make_float2(0.f, 0.f);
+    const Bsdf b = make_bsdf<-1>(sc, sc.materials[Q.material], texin_from(g));
+    DrawSrc rng; rng.state = 0; rng.list = q[i].rand; rng.idx = 0; rng.n = 8;
+    const float3 wo = mk3(Q.wo[0], Q.wo[1], Q.wo[2]), wi = mk3(Q.wi[0], Q.wi[1], Q.wi[2]);
+    BsdfSample s;
+    bsdf_sample<-1>(b, wo, rng, s);
+    SptBxdfResult R;
+    if (s.need_probe) { rng.next(); rng.next(); rng.next(); s.lobe = -1; } // no scene in the hook: probe cannot run
+    R.sample_wi[0] = s.wi.x; R.sample_wi[1] = s.wi.y; R.sample_wi[2] = s.wi.z;
+    R.sample_f[0] = s.f.x; R.sample_f[1] = s.f.y; R.sample_f[2] = s.f.z;
+    R.sample_pdf = s.pdf; R.sample_lobe = s.lobe; R.sample_dir = s.dir; R.n_rand_used = rng.idx;
+    const float3 f = bsdf_eval<-1>(b, wo, wi);
+    R.eval_f[0] = f.x; R.eval_f[1] = f.y; R.eval_f[2] = f.z; R.eval_pdf = bsdf_pdf<-1>(b, wo, wi);
+    R.is_delta = bsdf_is_delta<-1>(b) ? 1 : 0; R.bxdf_tag = b.tag;
+    out[i] = R;
+  }
+}
+
+namespace spt {
+void launch_logic(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st) { k_logic<<<grid, SPT_LOGIC_BLOCK, 0, st>>>(sc, P); }
+void launch_special(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st) { k_special<<<grid, SPT_BLOCK, 0, st>>>(sc, P); }
+void launch_generate(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st) { k_generate<<<grid, SPT_LOGIC_BLOCK, 0, st>>>(sc, P); }
+void launch_resolve(const long long* film, int n_pixels, float inv_spp, float* out_mean, uint8_t* out_rgb8, int grid, cudaStream_t st) {
+  k_resolve<<<grid, 256, 0, st>>>(film, n_pixels, inv_spp, out_mean, out_rgb8);
+}
+void launch_bxdf(const DScene& sc, const SptBxdfQuery* q, long long n, SptBxdfResult* out, int grid, cudaStream_t st) {
+  k_bxdf_batch<<<grid, SPT_BLOCK, 0, st>>>(sc, q, n, out);
+}
+void launch_shade(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st) {
+  if (mat >= 0 && mat <= 3) launch_shade_a(mat, sc, P, count, grid, st);
+  else if (mat >= 4 && mat <= 6) launch_shade_b(mat, sc, P, count, grid, st);
+  else launch_shade_c(mat, sc, P, count, grid, st);
+}
+} // namespace spt

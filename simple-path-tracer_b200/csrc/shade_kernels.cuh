@@ -1,0 +1,177 @@
+// shade_kernels.cuh — shade<MAT> kernels and the per-path register state shared with k_special (see wavefront.cuh for the stage chain).
+#pragma once
+#include "wavefront.cuh"
+
+#define SPT_BLOCK SPT_TRAV_BLOCK // the shade kernels share the shared-memory stack layout of the traversal (BSSRDF probe)
+
+// ---- per-path state in registers during shading ---------------------------------------------------------------------------
+struct PathRegs {
+  float3 ro, rd, thr;
+  float rtmin, last_pdf;
+  PathRng rng;
+  uint32_t pixel;
+  int depth, medium;
+};
+struct ShadowRay { float3 o, d, c; float tmin, tmax; bool emit; };
+
+SPT_D void load_path(const RenderParams& P, int slot, uint32_t flags, PathRegs& s, HitRec& hit) {
+  const float4 o4 = P.pool.ray_o[slot], d4 = P.pool.ray_d[slot], h4 = P.pool.hit[slot], t4 = P.pool.thr[slot];
+  s.ro = mk3(o4); s.rd = mk3(d4); s.rtmin = o4.w;
+  hit.t = h4.x; hit.u = h4.y; hit.v = h4.z; hit.tri = __float_as_int(h4.w); hit.prim = 0; hit.inst = P.pool.hit_inst[slot];
+  s.thr = mk3(t4); s.last_pdf = t4.w;
+  s.rng.state = P.pool.rng[slot];
+  s.pixel = P.pool.pixel[slot];
+  s.depth = (int)((flags >> 8) & 0xffu);
+  s.medium = (int)(flags >> 16) - 1;
+}
+// Russian roulette + depth count (pt.rs:195-206), then write the path back or mark its slot free.
+SPT_D void finish_bounce(const RenderParams& P, int slot, PathRegs& s, bool terminate) {
+  if (!terminate) {
+    if (!finite3(s.thr)) terminate = true;
+    else {
+      const float rr = s.rng.next();
+      const float p = clampf_(lum3(s.thr), 0.001f, 0.95f);
+      if (rr > p) terminate = true;
+      else { s.thr = s.thr * (1.0f / p); s.depth++; if (s.depth >= P.max_depth) terminate = true; }
+    }
+  }
+  if (terminate) { P.pool.flags[slot] = 0u; return; }
+  P.pool.ray_o[slot] = make_float4(s.ro.x, s.ro.y, s.ro.z, s.rtmin);
+  P.pool.ray_d[slot] = make_float4(s.rd.x, s.rd.y, s.rd.z, 0.f);
+  P.pool.thr[slot] = make_float4(s.thr.x, s.thr.y, s.thr.z, s.last_pdf);
+  P.pool.rng[slot] = s.rng.state;
+  P.pool.flags[slot] = 1u | ((uint32_t)s.depth << 8) | ((uint32_t)(s.medium + 1) << 16);
+}
+// Shadow-ray emission into the compacted queue, one atomic per warp.
+SPT_D void push_shadow(const RenderParams& P, const ShadowRay& sh, uint32_t pixel) {
+  const uint32_t qi = warp_reserve<uint32_t>(&P.ctr->it.sq, sh.emit);
+  if (sh.emit) {
+    P.sq.o[qi] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.tmin);
+    P.sq.d[qi] = make_float4(sh.d.x, sh.d.y, sh.d.z, sh.tmax);
+    P.sq.c[qi] = make_float4(sh.c.x, sh.c.y, sh.c.z, __uint_as_float(pixel));
+  }
+}
+
+// ---- shade<MAT>: surface hits of one material class (pt.rs:112-193) --------------------------------------------------------------
+template <int MAT> struct ShadeCfg { static constexpr int min_blocks = 3; };
+template <> struct ShadeCfg<0> { static constexpr int min_blocks = 4; };
+template <> struct ShadeCfg<1> { static constexpr int min_blocks = 4; };
+
+template <int MAT, bool COUNT>
+__global__ void __launch_bounds__(SPT_BLOCK, ShadeCfg<MAT>::min_blocks) k_shade(const DScene sc, const RenderParams P) {
+  constexpr bool PROBE = MAT < 0 || MAT == 7; // the BSSRDF probe ray needs the traversal stack
+  __shared__ uint2 s_stack[PROBE ? SPT_SSTACK : 1][PROBE ? SPT_TRAV_BLOCK : 1];
+  uint32_t nonfinite = 0, n_probe = 0;
+  TravCounters tc = {0, 0, 0};
+  constexpr int QI = MAT < 0 ? SPT_Q_GENERIC : MAT;
+  const uint32_t n = P.ctr->it.q[QI];
+  const uint32_t* queue = P.queue + (size_t)QI * P.pool.n;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int slot = (int)queue[i];
+    const uint32_t flags = P.pool.flags[slot];
+    PathRegs s; HitRec hit;
+    load_path(P, slot, flags, s, hit);
+    ShadowRay sh; sh.emit = false; sh.o = sh.d = sh.c = mk3(0.f); sh.tmin = sh.tmax = 0.f;
+    bool terminate = false;
+
+    HitGeom g;
+    load_hit(sc, s.ro, s.rd, hit, g);
+    if (s.depth == 0 && sc.has_image_tex) { // ray differentials exist only for camera rays (Q18)
+      const uint32_t k = P.pool.sample[slot];
+      PathRng r2; r2.state = rng_init(P.seed, s.pixel, k);
+      float ox, oy, x, y; pixel_offset(P, s.pixel, k, r2, ox, oy); film_xy(P, s.pixel, ox, oy, x, y);
+      const float aspect = (float)P.width / (float)P.height, ssi = 1.0f / sqrtf((float)P.spp);
+      const float3 eye = mk3(sc.camera.eye[0], sc.camera.eye[1], sc.camera.eye[2]);
+      calc_differential(g, eye, camera_dir(sc.camera, x + aspect / (float)P.width * ssi, y), eye, camera_dir(sc.camera, x, y + ssi / (float)P.height));
+    }
+    const DSurface sf = sc.surfaces[g.surface];
+    const TexIn tin = texin_from(g);
+    const Bsdf bsdf = make_bsdf<MAT>(sc, sc.materials[sf.material], tin);
+    Frame fr = surface_frame(sc, sf, s.rd, g, tin);
+    const float3 em = surface_emissive(sc, sf, tin);
+    if (lum3(em) > 0.0f) {
+      const float w = s.depth == 0 ? 1.0f : power_heuristic(s.last_pdf, pdf_shape_light(sc, s.ro, g, sf.double_sided != 0));
+      film_add(P, s.pixel, s.thr * em * w, nonfinite);
+    }
+    float3 po = g.p;
+    const float3 wo = to_local(fr, -s.rd);
+    BsdfSample bs;
+    bsdf_sample<MAT>(bsdf, wo, s.rng, bs);
+    bool dead_after_nee = false;
+    if constexpr (PROBE) {
+      if (bs.need_probe) { // Subsurface::sample, substrate.rs:231-333
+        float rand_u = s.rng.next();
+        const float rand_x = s.rng.next(), rand_y = s.rng.next();
+        float3 st, sb, sn;
+        if (rand_u < 0.5f) { rand_u = rand_u * 2.0f; st = fr.x; sb = fr.y; sn = fr.z; }
+        else if (rand_u < 0.75f) { rand_u = rand_u * 4.0f - 2.0f; st = fr.y; sb = fr.z; sn = fr.x; }
+        else { rand_u = rand_u * 4.0f - 3.0f; st = fr.z; sb = fr.x; sn = fr.y; }
+        const float sp_d = rand_u < 1.0f / 3.0f ? bsdf.s_d.x : (rand_u < 2.0f / 3.0f ? bsdf.s_d.y : bsdf.s_d.z);
+        const int ci = ss_cdf_lower_bound(sc.ss_cdf, rand_x);
+        bool ok = ci < 512;
+        float sample_r = -1.0f;
+        if (ok) {
+          const float y0 = sc.ss_cdf[2 * ci - 1], y1 = sc.ss_cdf[2 * ci + 1], x0 = sc.ss_cdf[2 * ci - 2], x1 = sc.ss_cdf[2 * ci];
+          const float t = (rand_x - y0) / (y1 - y0);
+          sample_r = (x1 * t + x0 * (1.0f - t)) * sp_d;
+        }
+        const float r_max = sc.ss_cdf[2 * 511] * sp_d;
+        ok = ok && !(sample_r < 0.0f);
+        if (ok) {
+          float sphi, cphi; sincos_2pi(rand_y, sphi, cphi);
+          const float sample_l = sqrtf(r_max * r_max + sample_r * sample_r);
+          const float3 start = po + st * cphi * sample_r + sb * sphi * sample_r + sn * sample_l;
+          HitRec ph; ph.t = 2.0f * sample_l; ph.u = ph.v = 0.f; ph.prim = -1; ph.inst = -1; ph.tri = -1;
+          n_probe++;
+          uint2 l_stack[SPT_LSTACK];
+          TravStack tst; tst.sh = &s_stack[0][threadIdx.x]; tst.lo = l_stack;
+          ok = traverse<false, COUNT>(sc, start, -sn, 1e-4f, ph, tc, tst);
+          if (ok) {
+            HitGeom pg; load_hit(sc, start, -sn, ph, pg);
+            const DSurface psf = sc.surfaces[pg.surface];
+            const Frame pfr = surface_frame(sc, psf, -sn, pg, texin_from(pg));
+            const float3 pi = pg.p;
+            const float3 spv = ss_sp(bsdf, len3(pi - po));
+            const float3 off = to_local(fr, pi - po), nl = to_local(fr, pg.n);
+            const float r_xy = sqrtf(off.x * off.x + off.y * off.y), r_yz = sqrtf(off.y * off.y + off.z * off.z), r_zx = sqrtf(off.z * off.z + off.x * off.x);
+            const float pdf_pi = 0.5f * fabsf(nl.z) * avg3(ss_sp(bsdf, r_xy)) + 0.25f * fabsf(nl.x) * avg3(ss_sp(bsdf, r_yz)) + 0.25f * fabsf(nl.y) * avg3(ss_sp(bsdf, r_zx));
+            float3 wi, fs; float ps;
+            sub_sample_diffuse<MAT>(bsdf, wo, s.rng, wi, fs, ps);
+            plastic_combine<MAT>(bsdf, wo, wi, fs, ps, LOBE_DIFFUSE, bs);
+            po = pi; fr = pfr;                 // pt.rs:147-151
+            s.thr *= spv / pdf_pi;
+          }
+        }
+        if (!ok) dead_after_nee = true; // sample has wi = 0, bxdf = 0: the path contributes nothing further
+      }
+    }
+    if (!bsdf_is_delta<MAT>(bsdf) && sc.n_lights > 0) { // pt.rs:158-179
+      LightSample ls;
+      sample_one_light(sc, po, s.rng, ls);
+      const float3 wi = to_local(fr, ls.dir);
+      const float3 f = bsdf_eval<MAT>(bsdf, wo, wi);
+      const float mat_pdf = bsdf_pdf<MAT>(bsdf, wo, wi);
+      if (ls.pdf != 0.0f && isfinite(ls.pdf)) {
+        const float w = ls.delta ? 1.0f : power_heuristic(ls.pdf, mat_pdf);
+        const float3 li = ls.L * f * fabsf(wi.z) * w / fmaxf(ls.pdf, 0.00001f);
+        sh.emit = true; sh.o = po; sh.d = ls.dir; sh.tmin = 1e-4f / fmaxf(fabsf(wi.z), 0.00001f); sh.tmax = ls.dist - 0.001f; sh.c = s.thr * li;
+      }
+    }
+    if (dead_after_nee) terminate = true;
+    else {
+      s.last_pdf = bs.pdf;
+      const float3 wi_world = to_world(fr, bs.wi);
+      s.ro = po; s.rd = wi_world; s.rtmin = 1e-4f / fmaxf(fabsf(bs.wi.z), 0.00001f);
+      s.thr *= bs.f * fabsf(bs.wi.z) / fmaxf(bs.pdf, 0.00001f);
+      const float hd = dot3(wi_world, fr.hemi); // Coordinate::in_expected_hemisphere, coord.rs:53-59
+      if (!(bs.dir == DIR_REFLECT ? hd >= 0.f : hd <= 0.f)) terminate = true;
+      else if (dot3(wi_world, g.n) < 0.f) s.medium = sf.double_sided ? -1 : sf.inside_medium; // pt.rs:190-192, surface.rs:105-111
+    }
+    push_shadow(P, sh, s.pixel);
+    finish_bounce(P, slot, s, terminate);
+  }
+  warp_sum_to(&P.ctr->nonfinite, nonfinite);
+  if (PROBE) warp_sum_to(&P.ctr->probe_rays, n_probe);
+  if (COUNT && PROBE) { warp_sum_to(&P.ctr->nodes, tc.nodes); warp_sum_to(&P.ctr->tris, tc.tris); warp_sum_to(&P.ctr->insts, tc.insts); }
+}
+

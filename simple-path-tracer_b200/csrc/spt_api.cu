@@ -7,7 +7,7 @@
 #include <new>
 #include "../../include/spt.h"
 #include "flatten.h"
-#include "kernels.cuh"
+#include "launch.h"
 
 namespace {
 
@@ -43,7 +43,7 @@ struct SptScene {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[2] = {nullptr, nullptr};
   cudaEvent_t sev[4] = {nullptr, nullptr, nullptr, nullptr}; // per-stage timing (SPT_RENDER_TIME_STAGES)
-  int occ_ext = 0, occ_con = 0, occ_shade = 0; // resident blocks per SM of the persistent kernels (occupancy API)
+  int occ_ext = 0, occ_con = 0, occ_bat = 0; // resident blocks per SM of the persistent kernels (occupancy API)
 };
 
 namespace {
@@ -64,11 +64,11 @@ int upload(SptScene* s, const std::vector<T>& v, const T** dptr) {
 // Grid of a persistent traversal kernel: `per_sm` resident blocks on every SM, fewer when there is little work.
 int persistent_grid(const SptContext* c, long long n_rays, int per_sm) {
   const long long want = (n_rays + SPT_FETCH_CHUNK - 1) / SPT_FETCH_CHUNK; // one warp per chunk is enough
-  const long long blocks = (want + (SPT_BLOCK / 32) - 1) / (SPT_BLOCK / 32);
+  const long long blocks = (want + (SPT_TRAV_BLOCK / 32) - 1) / (SPT_TRAV_BLOCK / 32);
   return (int)std::max<long long>(1, std::min<long long>(blocks, (long long)c->sm_count * per_sm));
 }
 int grid_for(const SptContext* c, long long n, int per_sm) {
-  long long blocks = (n + SPT_BLOCK - 1) / SPT_BLOCK;
+  long long blocks = (n + SPT_TRAV_BLOCK - 1) / SPT_TRAV_BLOCK;
   return (int)std::max<long long>(1, std::min<long long>(blocks, (long long)c->sm_count * per_sm));
 }
 
@@ -186,12 +186,12 @@ static int32_t batch_device(SptScene* s, const SptRay* d_rays, int64_t n, void* 
   const int64_t CH = 1ll << 30; // the fetch cursor of one launch is 32-bit
   for (int64_t off = 0; off < n; off += CH) {
     const uint32_t m = (uint32_t)std::min<int64_t>(CH, n - off);
-    const int grid = persistent_grid(s->ctx, m, 8);
+    if (!s->occ_bat) { CU(spt::occupancy_traversal(&s->occ_ext, &s->occ_con, &s->occ_bat)); s->occ_bat = std::max(1, s->occ_bat); }
+    const int grid = persistent_grid(s->ctx, m, s->occ_bat);
     CU(cudaMemsetAsync(s->batch_next, 0, sizeof(uint32_t), st));
     HitIO* ho = any ? nullptr : (HitIO*)d_out + off;
     uint8_t* oo = any ? (uint8_t*)d_out + off : nullptr;
-    if (!any) { if (count) k_batch<false, true><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4 + 2 * off, m, ho, oo, s->batch_next, s->ctr); else k_batch<false, false><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4 + 2 * off, m, ho, oo, s->batch_next, nullptr); }
-    else { if (count) k_batch<true, true><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4 + 2 * off, m, ho, oo, s->batch_next, s->ctr); else k_batch<true, false><<<grid, SPT_BLOCK, 0, st>>>(s->ds, r4 + 2 * off, m, ho, oo, s->batch_next, nullptr); }
+    spt::launch_batch(s->ds, r4 + 2 * off, m, ho, oo, s->batch_next, s->ctr, any, count, grid, st);
     CU(cudaGetLastError());
     launches++;
   }
@@ -233,31 +233,6 @@ int32_t spt_occluded_batch(SptScene* s, const SptRay* rays, int64_t n, uint8_t* 
 
 } // extern "C"
 
-// ---- BxDF test hook -----------------------------------------------------------------------------------------------
-namespace {
-__global__ void k_bxdf_batch(const DScene sc, const SptBxdfQuery* __restrict__ q, long long n, SptBxdfResult* __restrict__ out) {
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    const SptBxdfQuery Q = q[i];
-    HitGeom g; g.p = mk3(0.f); g.n = mk3(0, 0, 1); g.tan = mk3(1, 0, 0); g.bitan = mk3(0, 1, 0);
-    g.uv = make_float2(Q.texcoord[0], Q.texcoord[1]); g.duvdx = g.duvdy = make_float2(0.f, 0.f);
-    const Bsdf b = make_bsdf<-1>(sc, sc.materials[Q.material], texin_from(g));
-    DrawSrc rng; rng.state = 0; rng.list = q[i].rand; rng.idx = 0; rng.n = 8;
-    const float3 wo = mk3(Q.wo[0], Q.wo[1], Q.wo[2]), wi = mk3(Q.wi[0], Q.wi[1], Q.wi[2]);
-    BsdfSample s;
-    bsdf_sample<-1>(b, wo, rng, s);
-    SptBxdfResult R;
-    if (s.need_probe) { rng.next(); rng.next(); rng.next(); s.lobe = -1; } // no scene in the hook: probe cannot run
-    R.sample_wi[0] = s.wi.x; R.sample_wi[1] = s.wi.y; R.sample_wi[2] = s.wi.z;
-    R.sample_f[0] = s.f.x; R.sample_f[1] = s.f.y; R.sample_f[2] = s.f.z;
-    R.sample_pdf = s.pdf; R.sample_lobe = s.lobe; R.sample_dir = s.dir; R.n_rand_used = rng.idx;
-    const float3 f = bsdf_eval<-1>(b, wo, wi);
-    R.eval_f[0] = f.x; R.eval_f[1] = f.y; R.eval_f[2] = f.z; R.eval_pdf = bsdf_pdf<-1>(b, wo, wi);
-    R.is_delta = bsdf_is_delta<-1>(b) ? 1 : 0; R.bxdf_tag = b.tag;
-    out[i] = R;
-  }
-}
-} // namespace
-
 extern "C" int32_t spt_bxdf_batch(SptScene* s, const SptBxdfQuery* queries, int64_t n, SptBxdfResult* out) {
   if (!s || n < 0 || (n > 0 && (!queries || !out))) return fail(SPT_ERR_INVALID, "spt_bxdf_batch: bad argument");
   if (n == 0) return SPT_OK;
@@ -267,7 +242,7 @@ extern "C" int32_t spt_bxdf_batch(SptScene* s, const SptBxdfQuery* queries, int6
   CU(cudaMalloc(&dq, (size_t)n * sizeof(SptBxdfQuery)));
   if (cudaMalloc(&dr, (size_t)n * sizeof(SptBxdfResult)) != cudaSuccess) { cudaFree(dq); return fail(SPT_ERR_CUDA, "cudaMalloc failed"); }
   cudaMemcpyAsync(dq, queries, (size_t)n * sizeof(SptBxdfQuery), cudaMemcpyHostToDevice, s->stream);
-  k_bxdf_batch<<<grid_for(s->ctx, n, 8), SPT_BLOCK, 0, s->stream>>>(s->ds, dq, n, dr);
+  spt::launch_bxdf(s->ds, dq, n, dr, grid_for(s->ctx, n, 8), s->stream);
   cudaMemcpyAsync(out, dr, (size_t)n * sizeof(SptBxdfResult), cudaMemcpyDeviceToHost, s->stream);
   cudaError_t e = cudaStreamSynchronize(s->stream);
   cudaFree(dq); cudaFree(dr);
@@ -308,7 +283,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   const size_t n_px = (size_t)r->width * r->height;
   // ---- buffers
   int pool_n = r->pool_size > 0 ? r->pool_size : (1 << 20);
-  pool_n = std::max(SPT_BLOCK, (pool_n + SPT_BLOCK - 1) / SPT_BLOCK * SPT_BLOCK);
+  pool_n = std::max(SPT_TRAV_BLOCK, (pool_n + SPT_TRAV_BLOCK - 1) / SPT_TRAV_BLOCK * SPT_TRAV_BLOCK);
   const size_t per_slot = 4 * sizeof(float4) + sizeof(int32_t) + sizeof(uint64_t) + 3 * sizeof(uint32_t) + 3 * sizeof(float4) + SPT_NQ * sizeof(uint32_t);
   if (s->pool_n != pool_n) {
     cudaFree(s->pool_mem); s->pool_mem = nullptr; s->pool_n = 0;
@@ -356,8 +331,8 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   CU(cudaMemsetAsync(P.pool.hit_inst, 0xff, (size_t)pool_n * sizeof(int32_t), st));
   CU(cudaEventRecord(s->ev[0], st));
   if (!s->occ_ext) { // resident blocks per SM of the persistent kernels, from the occupancy API (register / shared-memory limits)
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->occ_ext, k_extend<false>, SPT_BLOCK, 0));
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->occ_con, k_connect<false>, SPT_BLOCK, 0));
+    CU(spt::occupancy_traversal(&s->occ_ext, &s->occ_con, &s->occ_bat));
+    s->occ_bat = std::max(1, s->occ_bat);
     s->occ_ext = std::max(1, s->occ_ext); s->occ_con = std::max(1, s->occ_con);
   }
   const int grid_ext = persistent_grid(s->ctx, pool_n, s->occ_ext), grid_con = persistent_grid(s->ctx, pool_n, s->occ_con);
@@ -370,18 +345,15 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   const uint32_t mats = P.sort_materials ? ds.mat_mask : 0u;
   const bool special = ds.has_medium || ds.env_tex != nullptr;
   auto iteration = [&]() {
-    k_logic<<<grid_logic, SPT_LOGIC_BLOCK, 0, st>>>(ds, P); launches++;
-    if (special) { k_special<<<grid_shade, SPT_BLOCK, 0, st>>>(ds, P); launches++; }
-#define SHADE(M) if (mats & (1u << M)) { k_shade<M, false><<<grid_shade, SPT_BLOCK, 0, st>>>(ds, P); launches++; }
-    SHADE(0) SHADE(1) SHADE(2) SHADE(3) SHADE(4) SHADE(5) SHADE(6)
-#undef SHADE
-    if (mats & (1u << 7)) { if (count) k_shade<7, true><<<grid_shade, SPT_BLOCK, 0, st>>>(ds, P); else k_shade<7, false><<<grid_shade, SPT_BLOCK, 0, st>>>(ds, P); launches++; }
-    if (!P.sort_materials) { if (count) k_shade<-1, true><<<grid_shade, SPT_BLOCK, 0, st>>>(ds, P); else k_shade<-1, false><<<grid_shade, SPT_BLOCK, 0, st>>>(ds, P); launches++; }
-    k_generate<<<grid_gen, SPT_LOGIC_BLOCK, 0, st>>>(ds, P); launches++;
+    spt::launch_logic(ds, P, grid_logic, st); launches++;
+    if (special) { spt::launch_special(ds, P, grid_shade, st); launches++; }
+    for (int m = 0; m < 8; m++) if (mats & (1u << m)) { spt::launch_shade(m, ds, P, count, grid_shade, st); launches++; }
+    if (!P.sort_materials) { spt::launch_shade(-1, ds, P, count, grid_shade, st); launches++; }
+    spt::launch_generate(ds, P, grid_gen, st); launches++;
     if (timed) cudaEventRecord(s->sev[1], st);
-    if (count) k_connect<true><<<grid_con, SPT_BLOCK, 0, st>>>(ds, P); else k_connect<false><<<grid_con, SPT_BLOCK, 0, st>>>(ds, P);
+    spt::launch_connect(ds, P, count, grid_con, st);
     if (timed) cudaEventRecord(s->sev[2], st);
-    if (count) k_extend<true><<<grid_ext, SPT_BLOCK, 0, st>>>(ds, P); else k_extend<false><<<grid_ext, SPT_BLOCK, 0, st>>>(ds, P);
+    spt::launch_extend(ds, P, count, grid_ext, st);
     launches += 2; iters++;
   };
   if (r->max_depth > 0 && P.total_samples > 0) {
@@ -414,7 +386,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
       if (s->h_ctr->it.live == 0) break;
     }
   }
-  k_resolve<<<grid_for(s->ctx, (long long)n_px * 3, 8), 256, 0, st>>>(s->film, (int)n_px, 1.0f / (float)spp, d_mean, d_rgb8);
+  spt::launch_resolve(s->film, (int)n_px, 1.0f / (float)spp, d_mean, d_rgb8, grid_for(s->ctx, (long long)n_px * 3, 8), st);
   launches++;
   CU(cudaEventRecord(s->ev[1], st));
   CU(cudaMemcpyAsync(s->h_ctr, s->ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, st));

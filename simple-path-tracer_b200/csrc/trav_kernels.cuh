@@ -1,0 +1,94 @@
+// trav_kernels.cuh — the traversal kernels: extend (closest hit), connect (any hit + film), caller ray batches.
+#pragma once
+#include "wavefront.cuh"
+
+#define SPT_BLOCK SPT_TRAV_BLOCK
+
+// ---- ray sources of the persistent traversal driver -------------------------------------------------------------
+struct ExtendSrc { // every live path of the pool: closest hit (pt.rs:49-50)
+  const RenderParams& P;
+  uint32_t n_rays;
+  SPT_D uint32_t total() const { return (uint32_t)P.pool.n; }
+  SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
+    if (!(P.pool.flags[i] & 1u)) return false;
+    const float4 o4 = P.pool.ray_o[i], d4 = P.pool.ray_d[i];
+    o = mk3(o4); d = mk3(d4); tmin = o4.w; tmax = FLT_MAX; // Intersection::default, intersection.rs:86-102
+    n_rays++;
+    return true;
+  }
+  SPT_D void store(uint32_t i, const HitRec& h) {
+    P.pool.hit[i] = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
+    P.pool.hit_inst[i] = h.inst;
+  }
+};
+struct ConnectSrc { // the queued shadow rays: any hit (pt.rs:81, :169); unoccluded contributions go to the film
+  const RenderParams& P;
+  uint32_t n, nonfinite;
+  SPT_D uint32_t total() const { return n; }
+  SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
+    const float4 o4 = P.sq.o[i], d4 = P.sq.d[i];
+    o = mk3(o4); d = mk3(d4); tmin = o4.w; tmax = d4.w;
+    return true;
+  }
+  SPT_D void store(uint32_t i, const HitRec& h) {
+    if (h.inst < 0) { const float4 c = P.sq.c[i]; film_add(P, __float_as_uint(c.w), mk3(c), nonfinite); }
+  }
+};
+
+template <bool COUNT>
+__global__ void __launch_bounds__(SPT_BLOCK) k_extend(const DScene sc, const RenderParams P) {
+  TravCounters tc = {0, 0, 0};
+  if (blockIdx.x == 0 && threadIdx.x == 0) { P.ctr->it.sq = 0; P.ctr->it.next_con = 0; } // connect of this iteration is done
+  ExtendSrc src{P, 0};
+  trace_persistent<false, COUNT>(sc, src, &P.ctr->it.next_ext, tc);
+  warp_sum_to(&P.ctr->ext_rays, src.n_rays);
+  if (COUNT) { warp_sum_to(&P.ctr->nodes, tc.nodes); warp_sum_to(&P.ctr->tris, tc.tris); warp_sum_to(&P.ctr->insts, tc.insts); }
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(SPT_BLOCK) k_connect(const DScene sc, const RenderParams P) {
+  TravCounters tc = {0, 0, 0};
+  ConnectSrc src{P, P.ctr->it.sq, 0};
+  trace_persistent<true, COUNT>(sc, src, &P.ctr->it.next_con, tc);
+  if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&P.ctr->shadow_rays, (unsigned long long)src.n);
+  warp_sum_to(&P.ctr->nonfinite, src.nonfinite);
+  if (COUNT) { warp_sum_to(&P.ctr->nodes, tc.nodes); warp_sum_to(&P.ctr->tris, tc.tris); warp_sum_to(&P.ctr->insts, tc.insts); }
+}
+
+// ---- seam B2 on caller-supplied ray batches -------------------------------------------------------------------
+
+struct BatchSrc {
+  const DScene& sc;
+  const float4* __restrict__ rays; // 2 per ray: (o, tmin) (d, tmax)
+  uint32_t n;
+  HitIO* __restrict__ hits;       // closest-hit output or null
+  uint8_t* __restrict__ occ;      // any-hit output or null
+  SPT_D uint32_t total() const { return n; }
+  SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
+    const float4 a = ldg4(rays + 2 * (size_t)i), b = ldg4(rays + 2 * (size_t)i + 1);
+    o = mk3(a); d = mk3(b); tmin = a.w; tmax = b.w;
+    return true;
+  }
+  SPT_D void store(uint32_t i, const HitRec& h) {
+    if (occ) { occ[i] = h.inst >= 0 ? 1 : 0; return; }
+    HitIO o; o.t = h.t; o.u = h.u; o.v = h.v; o.prim = h.prim; o.inst = h.inst;
+    if (h.inst >= 0 && h.tri < 0) { // sphere: report texcoords like Intersection::texcoords
+      const DInstance I = sc.inst[h.inst];
+      const float4 a = ldg4(rays + 2 * (size_t)i), b = ldg4(rays + 2 * (size_t)i + 1);
+      const float3 o2 = xmat_point(I.inv0, I.inv1, I.inv2, mk3(a)), d2 = xmat_vec(I.inv0, I.inv1, I.inv2, mk3(b));
+      const float4 cr = sc.spheres[I.root];
+      const float2 uv = sphere_uv((xpoint_at(o2, d2, h.t) - mk3(cr)) / cr.w);
+      o.u = uv.x; o.v = uv.y;
+    }
+    hits[i] = o;
+  }
+};
+
+template <bool ANY, bool COUNT>
+__global__ void __launch_bounds__(SPT_BLOCK) k_batch(const DScene sc, const float4* __restrict__ rays, uint32_t n, HitIO* __restrict__ hits,
+                                                     uint8_t* __restrict__ occ, uint32_t* next, DevCounters* ctr) {
+  TravCounters tc = {0, 0, 0};
+  BatchSrc src{sc, rays, n, hits, occ};
+  trace_persistent<ANY, COUNT>(sc, src, next, tc);
+  if (COUNT && ctr) { warp_sum_to(&ctr->nodes, tc.nodes); warp_sum_to(&ctr->tris, tc.tris); warp_sum_to(&ctr->insts, tc.insts); }
+}

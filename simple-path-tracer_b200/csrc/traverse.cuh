@@ -17,7 +17,7 @@
 // leave lanes idle; all lanes of a warp advance in rounds of exactly one node step followed by the leaf work that
 // node produced (triangles / instances), which keeps the 200-instruction node step converged across the warp.
 #pragma once
-#include "scene.h"
+#include "launch.h"
 #include "vecmath.cuh"
 
 struct HitRec {
@@ -27,11 +27,10 @@ struct HitRec {
 };
 struct TravCounters { uint32_t nodes, tris, insts; };
 
-#define SPT_TRAV_BLOCK 128  // threads per block of every traversal kernel
 #define SPT_SSTACK 16       // stack entries per thread in shared memory
 #define SPT_LSTACK 32       // overflow entries in local memory (untouched unless a ray goes deeper than SPT_SSTACK)
-#ifndef SPT_FETCH_CHUNK
-#define SPT_FETCH_CHUNK 256 // rays a warp reserves per global atomic
+#ifndef SPT_FETCH_STATIC
+#define SPT_FETCH_STATIC 0   // 1: chunks dealt round-robin to warps instead of a global atomic cursor
 #endif
 #ifndef SPT_FETCH_MIN_IDLE
 #define SPT_FETCH_MIN_IDLE 6 // refill the warp once this many lanes are without a ray
@@ -48,7 +47,7 @@ SPT_D void ray_setup(RaySetup& r, float3 o, float3 d) {
   float dx = fabsf(d.x) < eps ? copysignf(eps, d.x) : d.x;
   float dy = fabsf(d.y) < eps ? copysignf(eps, d.y) : d.y;
   float dz = fabsf(d.z) < eps ? copysignf(eps, d.z) : d.z;
-  r.idir = mk3(1.0f / dx, 1.0f / dy, 1.0f / dz);
+  r.idir = mk3(__frcp_rn(dx), __frcp_rn(dy), __frcp_rn(dz)); // only the (conservative) box tests use it
   uint32_t oct = (d.x < 0.f ? 4u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 1u : 0u);
   r.octinv4 = (7u - oct) * 0x01010101u;
 }
@@ -149,101 +148,110 @@ struct Trav {
   float3 ow, dw; // the world-space ray (core/ray.rs); r holds the ray of the current space (world or object)
   float tmin;
   RaySetup r;
+  float3 widir; uint32_t woct; // idir / octant of the world-space ray, restored when a BLAS is left
   HitRec hit;    // hit.t doubles as the running t_max (Intersection::t, intersection.rs:21-26)
-  uint2 ng, tg;  // current node group / primitive group
+  uint2 ng, tg;  // pending node group / primitive group of the current space (either may be empty)
   int sp, blas_base, cur_inst;
 };
 SPT_D void trav_begin(Trav& T, float3 o, float3 d, float tmin, float tmax) {
   T.ow = o; T.dw = d; T.tmin = tmin;
   ray_setup(T.r, o, d);
+  T.widir = T.r.idir; T.woct = T.r.octinv4;
   T.hit.t = tmax; T.hit.u = T.hit.v = 0.f; T.hit.prim = -1; T.hit.inst = -1; T.hit.tri = -1; // Intersection::default
   T.ng = make_uint2(0u, 0x80000000u); T.tg = make_uint2(0u, 0u);
   T.sp = 0; T.blas_base = 0; T.cur_inst = -1;
 }
+SPT_D bool trav_has_node(const Trav& T) { return T.ng.y > 0x00ffffffu; }
+SPT_D bool trav_has_leaf(const Trav& T) { return T.tg.y != 0u; }
 
-// One round: exactly one node step (T.ng holds at least one pending child on entry), then all the leaf work up to
-// the next node step.  Returns true when the ray is finished (ANY: also when an occluder was found, hit.inst = 0).
-// ANY = false: closest hit in (tmin, hit.t) -> hit.  ANY = true: any primitive in (tmin, tmax = hit.t).
+// Node step: take the nearest pending child of T.ng, intersect its 8 children -> new T.ng / T.tg.
+template <bool COUNT>
+SPT_D void trav_node(const DScene& sc, Trav& T, const TravStack& st, TravCounters& cnt) {
+  const uint32_t bit = bfind_u32(T.ng.y);
+  const uint32_t base = T.ng.x, imask = T.ng.y;
+  T.ng.y &= ~(1u << bit);
+  if (T.ng.y > 0x00ffffffu) st.push(T.sp, T.ng);
+  const uint32_t slot = (bit - 24u) ^ (T.r.octinv4 & 0xffu);
+  const uint32_t rel = __popc(imask & ~(0xffffffffu << slot));
+  if (COUNT) cnt.nodes++;
+  node_children(sc.nodes, base + rel, T.r, T.tmin, T.hit.t, T.ng, T.tg);
+}
+// One triangle of T.tg against the object-space ray (BLAS leaf or small mesh).  Returns true when ANY found an occluder.
 template <bool ANY, bool COUNT>
-SPT_D bool trav_round(const DScene& sc, Trav& T, const TravStack& st, TravCounters& cnt) {
-  {
-    const uint32_t bit = bfind_u32(T.ng.y);
-    const uint32_t base = T.ng.x, imask = T.ng.y;
-    T.ng.y &= ~(1u << bit);
-    if (T.ng.y > 0x00ffffffu) st.push(T.sp, T.ng);
-    const uint32_t slot = (bit - 24u) ^ (T.r.octinv4 & 0xffu);
-    const uint32_t rel = __popc(imask & ~(0xffffffffu << slot));
-    if (COUNT) cnt.nodes++;
-    node_children(sc.nodes, base + rel, T.r, T.tmin, T.hit.t, T.ng, T.tg);
+SPT_D bool trav_tri(const DScene& sc, Trav& T, TravCounters& cnt) {
+  const uint32_t k = bfind_u32(T.tg.y);
+  T.tg.y &= ~(1u << k);
+  const uint32_t pidx = T.tg.x + k;
+  if (COUNT) cnt.tris++;
+  float t, v, w; int tid;
+  if (tri_test(sc.tris, pidx, T.r.o, T.r.d, t, v, w, tid) && t > T.tmin && t < T.hit.t) { // triangle.rs:177-187
+    if (ANY) { T.hit.inst = 0; return true; }
+    T.hit.t = t; T.hit.u = v; T.hit.v = w; T.hit.prim = tid; T.hit.tri = (int)pidx; T.hit.inst = T.cur_inst;
   }
-  for (;;) {
-    while (T.tg.y != 0u) {
-      const uint32_t k = bfind_u32(T.tg.y);
-      T.tg.y &= ~(1u << k);
-      const uint32_t pidx = T.tg.x + k;
-      if (T.cur_inst < 0) { // TLAS leaf: an instance (instance.rs:89-109)
-        const int iid = sc.tlas_inst[pidx];
-        const float4* ip = reinterpret_cast<const float4*>(sc.inst + iid);
-        const float4 r0 = ldg4(ip), r1 = ldg4(ip + 1), r2 = ldg4(ip + 2), mt = ldg4(ip + 3);
-        if (COUNT) cnt.insts++;
-        const float3 o2 = xmat_point(r0, r1, r2, T.ow), d2 = xmat_vec(r0, r1, r2, T.dw);
-        const int kind = __float_as_int(mt.x), root = __float_as_int(mt.y);
-        if (kind == 0) { // sphere
-          if (COUNT) cnt.tris++;
-          float mn, mx;
-          if (sphere_roots(ldg4(sc.spheres + root), o2, d2, mn, mx)) {
-            if (ANY) { if (mn < T.hit.t && mx > T.tmin) { T.hit.inst = 0; return true; } } // sphere.rs:51-57
-            else {
-              const float t = mn < T.tmin ? mx : mn;                                      // sphere.rs:59-63
-              if (T.tmin < t && t < T.hit.t) { T.hit.t = t; T.hit.u = 0.f; T.hit.v = 0.f; T.hit.prim = 0; T.hit.tri = -1; T.hit.inst = iid; }
-            }
-          }
-        } else if (kind & 2) { // small mesh: its few triangles directly, same object-space ray as the BLAS would see
-          const int n = kind >> 8;
-          for (int j = 0; j < n; j++) {
-            if (COUNT) cnt.tris++;
-            float t, v, w; int tid;
-            if (tri_test(sc.tris, (uint32_t)(root + j), o2, d2, t, v, w, tid) && t > T.tmin && t < T.hit.t) {
-              if (ANY) { T.hit.inst = 0; return true; }
-              T.hit.t = t; T.hit.u = v; T.hit.v = w; T.hit.prim = tid; T.hit.tri = root + j; T.hit.inst = iid;
-            }
-          }
-        } else { // enter the BLAS with the object-space ray
-          if (T.tg.y != 0u) st.push(T.sp, T.tg);
-          if (T.ng.y > 0x00ffffffu) st.push(T.sp, T.ng);
-          T.blas_base = T.sp; T.cur_inst = iid;
-          ray_setup(T.r, o2, d2);
-          T.ng = make_uint2((uint32_t)root, 0x80000000u);
-          T.tg = make_uint2(0u, 0u);
-          return false;
-        }
-      } else {
-        if (COUNT) cnt.tris++;
-        float t, v, w; int tid;
-        if (tri_test(sc.tris, pidx, T.r.o, T.r.d, t, v, w, tid)) {
-          if (t > T.tmin && t < T.hit.t) { // triangle.rs:177-187
-            if (ANY) { T.hit.inst = 0; return true; }
-            T.hit.t = t; T.hit.u = v; T.hit.v = w; T.hit.prim = tid; T.hit.tri = (int)pidx; T.hit.inst = T.cur_inst;
-          }
-        }
+  return false;
+}
+// One instance of T.tg (a TLAS leaf, instance.rs:89-109): sphere test, or switch to the object-space ray and queue the
+// instance's BLAS root (mesh) or its few triangles (small mesh).  Returns true when ANY found an occluder.
+template <bool ANY, bool COUNT>
+SPT_D bool trav_inst(const DScene& sc, Trav& T, const TravStack& st, TravCounters& cnt) {
+  const uint32_t k = bfind_u32(T.tg.y);
+  T.tg.y &= ~(1u << k);
+  const int iid = sc.tlas_inst[T.tg.x + k];
+  const float4* ip = reinterpret_cast<const float4*>(sc.inst + iid);
+  const float4 r0 = ldg4(ip), r1 = ldg4(ip + 1), r2 = ldg4(ip + 2), mt = ldg4(ip + 3);
+  if (COUNT) cnt.insts++;
+  const float3 o2 = xmat_point(r0, r1, r2, T.ow), d2 = xmat_vec(r0, r1, r2, T.dw);
+  const int kind = __float_as_int(mt.x), root = __float_as_int(mt.y);
+  if (kind == 0) { // sphere
+    if (COUNT) cnt.tris++;
+    float mn, mx;
+    if (sphere_roots(ldg4(sc.spheres + root), o2, d2, mn, mx)) {
+      if (ANY) { if (mn < T.hit.t && mx > T.tmin) { T.hit.inst = 0; return true; } } // sphere.rs:51-57
+      else {
+        const float t = mn < T.tmin ? mx : mn;                                      // sphere.rs:59-63
+        if (T.tmin < t && t < T.hit.t) { T.hit.t = t; T.hit.u = 0.f; T.hit.v = 0.f; T.hit.prim = 0; T.hit.tri = -1; T.hit.inst = iid; }
       }
     }
-    if (T.ng.y > 0x00ffffffu) return false;
-    if (T.cur_inst >= 0 && T.sp == T.blas_base) { T.cur_inst = -1; ray_setup(T.r, T.ow, T.dw); }
-    if (T.sp == 0) return true;
-    T.ng = st.pop(T.sp);
-    if (T.ng.y > 0x00ffffffu) return false;
-    T.tg = T.ng; T.ng = make_uint2(0u, 0u); // a postponed primitive group: test it now, the next round starts at a node
+    return false;
   }
+  if (T.tg.y != 0u) st.push(T.sp, T.tg);
+  if (T.ng.y > 0x00ffffffu) st.push(T.sp, T.ng);
+  T.blas_base = T.sp; T.cur_inst = iid;
+  if (kind & 2) { // small mesh: its triangles become the pending primitive group, no BLAS node step
+    T.r.o = o2; T.r.d = d2;
+    T.ng = make_uint2(0u, 0u);
+    T.tg = make_uint2((uint32_t)root, (1u << (kind >> 8)) - 1u);
+  } else {
+    ray_setup(T.r, o2, d2);
+    T.ng = make_uint2((uint32_t)root, 0x80000000u);
+    T.tg = make_uint2(0u, 0u);
+  }
+  return false;
+}
+// Called when neither a node nor a primitive group is pending: leave the BLAS if it is exhausted, pop the next group.
+// Returns true when the ray is finished.
+SPT_D bool trav_pop(Trav& T, const TravStack& st) {
+  if (T.cur_inst >= 0 && T.sp == T.blas_base) { T.cur_inst = -1; T.r.o = T.ow; T.r.d = T.dw; T.r.idir = T.widir; T.r.octinv4 = T.woct; }
+  if (T.sp == 0) return true;
+  const uint2 e = st.pop(T.sp);
+  if (e.y > 0x00ffffffu) { T.ng = e; T.tg = make_uint2(0u, 0u); } else { T.tg = e; T.ng = make_uint2(0u, 0u); }
+  return false;
 }
 
-// Single-ray query (used inside shading for the BSSRDF probe): runs the rounds back to back.
+// Single-ray query (used inside shading for the BSSRDF probe).
+// ANY = false: closest hit in (tmin, hit.t) -> hit.  ANY = true: any primitive in (tmin, tmax = hit.t).
 template <bool ANY, bool COUNT>
 SPT_D bool traverse(const DScene& sc, float3 ow, float3 dw, float tmin, HitRec& hit, TravCounters& cnt, const TravStack& st) {
   if (sc.tlas_empty) return false;
   Trav T;
   trav_begin(T, ow, dw, tmin, hit.t);
-  while (!trav_round<ANY, COUNT>(sc, T, st, cnt)) {}
+  for (;;) {
+    if (trav_has_node(T)) trav_node<COUNT>(sc, T, st, cnt);
+    bool stop = false;
+    while (T.tg.y != 0u && !stop) stop = T.cur_inst >= 0 ? trav_tri<ANY, COUNT>(sc, T, cnt) : trav_inst<ANY, COUNT>(sc, T, st, cnt);
+    if (stop) break;
+    if (!trav_has_node(T) && T.tg.y == 0u && trav_pop(T, st)) break;
+  }
   hit = T.hit;
   return hit.inst >= 0;
 }
@@ -254,6 +262,16 @@ SPT_D bool traverse(const DScene& sc, float3 ow, float3 dw, float tmin, HitRec& 
 //   void store(uint32_t i, const HitRec& h);                           closest hit (inst = -1: miss) / ANY: inst = 0 occluded
 // `next` is a zero-initialised device counter of this launch.  Must be called by all threads of a block of
 // SPT_TRAV_BLOCK threads (uses a static shared-memory stack).
+//
+// Every round the whole warp passes through the same fixed chain of stages, each executed once by all the lanes that
+// have that kind of work pending, in the order a single ray needs them:
+//   refill -> pop (stack / leave BLAS / finish) -> node step -> instance visit -> triangle test (x SPT_TRI_PER_ROUND)
+// so a lane can advance through several stages in one round, no lane ever waits for another lane's leaf work, and
+// lanes doing the same kind of work execute it together instead of drifting apart under independent thread scheduling.
+// A lane drains its pending primitive group before it takes its next node step (same order as a depth-first loop).
+#ifndef SPT_TRI_PER_ROUND
+#define SPT_TRI_PER_ROUND 2
+#endif
 template <bool ANY, bool COUNT, class Src>
 SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCounters& cnt) {
   __shared__ uint2 s_stack[SPT_SSTACK][SPT_TRAV_BLOCK];
@@ -261,15 +279,26 @@ SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCoun
   TravStack st; st.sh = &s_stack[0][threadIdx.x]; st.lo = l_stack;
   const uint32_t total = src.total(), lane = threadIdx.x & 31u, FULL = 0xffffffffu;
   uint32_t w_next = 0, w_end = 0, idx = 0;
+#if SPT_FETCH_STATIC
+  uint32_t chunk = blockIdx.x * (SPT_TRAV_BLOCK / 32) + (threadIdx.x >> 5);
+  (void)next;
+#endif
   bool exhausted = false, has = false;
   Trav T;
+  T.ng = T.tg = make_uint2(0u, 0u); T.cur_inst = -1; T.sp = 0;
   for (;;) {
+    // ---- refill
     const uint32_t idle = __ballot_sync(FULL, !has);
     if (idle == FULL || __popc(idle) >= SPT_FETCH_MIN_IDLE) {
-      if (w_next >= w_end && !exhausted) { // reserve the next chunk for this warp
+      if (w_next >= w_end && !exhausted) { // next chunk of this warp
+#if SPT_FETCH_STATIC
+        const uint32_t base = chunk * (uint32_t)SPT_FETCH_CHUNK; // chunks dealt round-robin over the warps of the grid: no atomics
+        chunk += gridDim.x * (SPT_TRAV_BLOCK / 32);
+#else
         uint32_t base = 0;
         if (lane == 0) base = atomicAdd(next, (uint32_t)SPT_FETCH_CHUNK);
         base = __shfl_sync(FULL, base, 0);
+#endif
         if (base >= total) exhausted = true;
         else { w_next = base; w_end = min(base + (uint32_t)SPT_FETCH_CHUNK, total); }
       }
@@ -288,7 +317,18 @@ SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCoun
       }
       w_next += take;
     }
-    if (has && trav_round<ANY, COUNT>(sc, T, st, cnt)) { src.store(idx, T.hit); has = false; }
+    bool fin = false;
+    // ---- pop: nothing pending -> leave the BLAS / next stack entry / ray finished
+    if (has && !trav_has_node(T) && !trav_has_leaf(T)) fin = trav_pop(T, st);
+    // ---- node step
+    if (has && !fin && trav_has_node(T) && !trav_has_leaf(T)) trav_node<COUNT>(sc, T, st, cnt);
+    // ---- instance visit (TLAS leaf)
+    if (has && !fin && trav_has_leaf(T) && T.cur_inst < 0) fin = trav_inst<ANY, COUNT>(sc, T, st, cnt);
+    // ---- triangle tests (BLAS leaf / small mesh)
+#pragma unroll
+    for (int k = 0; k < SPT_TRI_PER_ROUND; k++)
+      if (has && !fin && trav_has_leaf(T) && T.cur_inst >= 0) fin = trav_tri<ANY, COUNT>(sc, T, cnt);
+    if (fin) { src.store(idx, T.hit); has = false; }
   }
 }
 

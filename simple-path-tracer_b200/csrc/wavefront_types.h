@@ -1,0 +1,49 @@
+// wavefront_types.h — plain structs shared by the host render loop (spt_api.cu) and the wavefront kernels.
+#pragma once
+#include <stdint.h>
+#include <cuda_runtime.h>
+
+#define SPT_NQ 10        // shade queues: 0..7 = material tag, 8 = special (medium / environment), 9 = unsorted surfaces
+#define SPT_Q_SPECIAL 8
+#define SPT_Q_GENERIC 9
+
+struct PathPool { // SoA over `n` slots
+  float4* ray_o;    // origin.xyz, t_min
+  float4* ray_d;    // direction.xyz, -
+  float4* hit;      // t, u, v, global triangle index (int bits; -1 = sphere)
+  int32_t* hit_inst;
+  float4* thr;      // throughput.rgb, last_sample_pdf
+  uint64_t* rng;
+  uint32_t* pixel;  // pixel index j*W+i
+  uint32_t* sample; // sample index k within the pixel
+  uint32_t* flags;  // bit0 alive | depth << 8 | (medium+1) << 16
+  int32_t n;
+};
+struct ShadowQueue { float4* o; float4* d; float4* c; }; // o.xyz,tmin | d.xyz,tmax | contrib.rgb,pixel
+struct IterCounters { // per-iteration device counters; each is zeroed by a kernel that runs between its consumer and its next producer
+  uint32_t q[SPT_NQ];   // shade-queue fill      (producer: logic/special, consumers: special/shade, zeroed by generate)
+  uint32_t sq;          // shadow-queue fill     (producer: special/shade, consumer: connect, zeroed by extend)
+  uint32_t live;        // live slots after generate (read by the host; zeroed by logic)
+  uint32_t next_ext;    // ray-fetch cursor of extend  (zeroed by logic)
+  uint32_t next_con;    // ray-fetch cursor of connect (zeroed by extend)
+  uint32_t pad[2];
+};
+struct DevCounters { // device-side totals of one render
+  unsigned long long cursor;      // next camera-sample ordinal
+  unsigned long long paths, ext_rays, shadow_rays, probe_rays, nonfinite, nodes, tris, insts;
+  IterCounters it;
+};
+struct RenderParams {
+  PathPool pool;
+  ShadowQueue sq;
+  uint32_t* queue;   // SPT_NQ arrays of pool.n slot ids
+  DevCounters* ctr;
+  long long* film; // 3 per pixel
+  const uint32_t* tiles; // owned tile ids
+  int32_t n_tiles, tiles_x, tile_w, tile_h;
+  int32_t width, height, max_depth;
+  int32_t sampler, spp, div_x, div_y;
+  int32_t sort_materials; // 0: every surface hit goes to the generic queue (SPT_RENDER_NO_SORT)
+  uint64_t seed;
+  unsigned long long total_samples; // n_tiles * tile_w * tile_h * spp
+};
