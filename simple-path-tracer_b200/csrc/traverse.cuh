@@ -47,7 +47,7 @@ SPT_D void ray_setup(RaySetup& r, float3 o, float3 d) {
   float dx = fabsf(d.x) < eps ? copysignf(eps, d.x) : d.x;
   float dy = fabsf(d.y) < eps ? copysignf(eps, d.y) : d.y;
   float dz = fabsf(d.z) < eps ? copysignf(eps, d.z) : d.z;
-  r.idir = mk3(__frcp_rn(dx), __frcp_rn(dy), __frcp_rn(dz)); // only the (conservative) box tests use it
+  r.idir = mk3(__fdividef(1.0f, dx), __fdividef(1.0f, dy), __fdividef(1.0f, dz)); // approximate (1 ulp): only the conservative box tests use it
   uint32_t oct = (d.x < 0.f ? 4u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 1u : 0u);
   r.octinv4 = (7u - oct) * 0x01010101u;
 }
@@ -87,7 +87,7 @@ SPT_D void node_children(const float4* __restrict__ nodes, uint32_t node_index, 
       const float t0y = fmaf((float)((neary >> sh) & 0xff), ay, by), t1y = fmaf((float)((fary >> sh) & 0xff), ay, by);
       const float t0z = fmaf((float)((nearz >> sh) & 0xff), az, bz), t1z = fmaf((float)((farz >> sh) & 0xff), az, bz);
       const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
-      const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax)) * 1.0000005f; // conservative against rounding
+      const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax)) * 1.000002f; // conservative against rounding (incl. the approximate 1/d)
       if (cmin <= cmax) hitmask |= ((cb4 >> sh) & 0xffu) << ((bit4 >> sh) & 0xffu);
     }
   }
@@ -214,6 +214,20 @@ SPT_D bool trav_inst(const DScene& sc, Trav& T, const TravStack& st, TravCounter
     }
     return false;
   }
+#if SPT_SMALL_INLINE
+  if (kind & 2) { // small mesh: test its few triangles right here with the object-space ray; the TLAS state is untouched
+    const int n = kind >> 8;
+    for (int j = 0; j < n; j++) {
+      if (COUNT) cnt.tris++;
+      float t, v, w; int tid;
+      if (tri_test(sc.tris, (uint32_t)(root + j), o2, d2, t, v, w, tid) && t > T.tmin && t < T.hit.t) {
+        if (ANY) { T.hit.inst = 0; return true; }
+        T.hit.t = t; T.hit.u = v; T.hit.v = w; T.hit.prim = tid; T.hit.tri = root + j; T.hit.inst = iid;
+      }
+    }
+    return false;
+  }
+#endif
   if (T.tg.y != 0u) st.push(T.sp, T.tg);
   if (T.ng.y > 0x00ffffffu) st.push(T.sp, T.ng);
   T.blas_base = T.sp; T.cur_inst = iid;
@@ -272,6 +286,15 @@ SPT_D bool traverse(const DScene& sc, float3 ow, float3 dw, float tmin, HitRec& 
 #ifndef SPT_TRI_PER_ROUND
 #define SPT_TRI_PER_ROUND 2
 #endif
+#ifndef SPT_INST_PER_ROUND
+#define SPT_INST_PER_ROUND 1
+#endif
+#ifndef SPT_STAGE_ORDER
+#define SPT_STAGE_ORDER 0   // 1: an extra instance stage before the node step (a BLAS entered there gets its root step in the same round)
+#endif
+#ifndef SPT_SMALL_INLINE
+#define SPT_SMALL_INLINE 0  // 1: small meshes are tested inside the instance stage instead of becoming a pending triangle group
+#endif
 template <bool ANY, bool COUNT, class Src>
 SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCounters& cnt) {
   __shared__ uint2 s_stack[SPT_SSTACK][SPT_TRAV_BLOCK];
@@ -320,10 +343,15 @@ SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCoun
     bool fin = false;
     // ---- pop: nothing pending -> leave the BLAS / next stack entry / ray finished
     if (has && !trav_has_node(T) && !trav_has_leaf(T)) fin = trav_pop(T, st);
+#if SPT_STAGE_ORDER == 1
+    if (has && !fin && trav_has_leaf(T) && T.cur_inst < 0) fin = trav_inst<ANY, COUNT>(sc, T, st, cnt);
+#endif
     // ---- node step
     if (has && !fin && trav_has_node(T) && !trav_has_leaf(T)) trav_node<COUNT>(sc, T, st, cnt);
     // ---- instance visit (TLAS leaf)
-    if (has && !fin && trav_has_leaf(T) && T.cur_inst < 0) fin = trav_inst<ANY, COUNT>(sc, T, st, cnt);
+#pragma unroll
+    for (int k = 0; k < SPT_INST_PER_ROUND; k++)
+      if (has && !fin && trav_has_leaf(T) && T.cur_inst < 0) fin = trav_inst<ANY, COUNT>(sc, T, st, cnt);
     // ---- triangle tests (BLAS leaf / small mesh)
 #pragma unroll
     for (int k = 0; k < SPT_TRI_PER_ROUND; k++)
