@@ -169,7 +169,7 @@ def main():
         sampler.start()
     barrier()
     t0 = time.perf_counter()
-    stats = [step(i + 1, abi.RENDER_TIME_STAGES) for i in range(args.steps)]
+    stats = [step(i + 1) for i in range(args.steps)]
     barrier()
     elapsed = time.perf_counter() - t0
     tt = torch.tensor([elapsed], dtype=torch.float64, device=dev)
@@ -209,32 +209,42 @@ def main():
             dist.destroy_process_group()
         return
     # ---- roofline of the dominant kernel (extend = closest-hit traversal), rank 0
+    # One extra step with per-stage CUDA events on the library's stream (it synchronises every iteration, so it is
+    # kept out of the timed region), and one short counting step for the mean nodes / triangles / instances per ray.
     peaks, peak_src = load_peaks()
+    s0 = sc.render_device(fb.data_ptr(), w, h, seed=1, flags=abi.RENDER_TIME_STAGES, **kw)
     cst = sc.render_device(fb.data_ptr(), w, h, seed=1, flags=abi.RENDER_COUNT_TRAVERSAL,
                            **dict(kw, spp=max(1, min(spp, 8))))
     n_rays = cst["ext_rays"] + cst["shadow_rays"] + cst["probe_rays"]
     n_node, n_tri, n_inst = cst["nodes_visited"] / n_rays, cst["tris_tested"] / n_rays, cst["insts_visited"] / n_rays
     b_ray = 52.0 + 80.0 * n_node + 48.0 * n_tri + 64.0 * n_inst          # SURVEY §8d algorithmic bytes per traced ray
-    s0 = stats[-1]
     ext_launches = s0["iterations"]
     ext_seconds = s0["seconds_stage"][1]
     rays_per_launch = s0["ext_rays"] / max(1, ext_launches)
     achieved = rays_per_launch * b_ray / max(ext_seconds / max(1, ext_launches), 1e-12) / 1e9
+    traffic = None
+    try:  # dram__bytes_read.sum + dram__bytes_write.sum of one k_extend launch from the committed ncu --set full capture
+        with open(os.path.join(ROOT, "profiles", "r01_ncu_extend_traffic.json")) as fh:
+            traffic = json.load(fh).get("dram_bytes_per_launch")
+    except OSError:
+        pass
+    pool_slots = args.pool or min(1 << 22, max(1 << 16, w * h * spp))
     roofline = {"bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
                 "bytes_per_ray": b_ray, "nodes_per_ray": n_node, "tris_per_ray": n_tri, "insts_per_ray": n_inst,
                 "rays_per_launch": rays_per_launch, "avg_launch_ms": 1e3 * ext_seconds / max(1, ext_launches),
+                "grays_per_s": rays_per_launch / max(ext_seconds / max(1, ext_launches), 1e-12) / 1e9,
                 "stage_seconds": {"extend": s0["seconds_stage"][1], "shade": s0["seconds_stage"][2], "connect": s0["seconds_stage"][3],
                                   "total": s0["seconds_total"]},
-                "note": "scene working set (%.2f MB) is L2-resident: the HBM figure is the contract's denominator, the binding roof is L2/latency" % (info["bytes_total"] / 1e6)}
+                "note": "scene working set (%.2f MB) is L2-resident: the HBM figure is the contract's denominator, the binding roof is instruction issue (ncu: issue-active 73 %%, 13/32 active lanes)" % (info["bytes_total"] / 1e6)}
     out = {
         "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": W,
         "ms_per_step": 1e3 * elapsed / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {w}x{h} @ {spp} spp, max_depth 8, recurrence sampler, box r=0.5",
                    "scene": "bunny_5k x3 (conductor, pbr_metallic iso+aniso) + room + emissive quad, power_is MIS" if args.workload == "c2" else args.workload,
-                   "parallelism": f"tiles{world}", "pool_slots": s0 and (args.pool or 1 << 20),
-                   "l2_policy": "per-step working set (path pool 143 MB + film) exceeds L2; no explicit flush"},
+                   "parallelism": f"tiles{world}", "pool_slots": pool_slots,
+                   "l2_policy": "per-step working set (path pool %d MB + film %d MB) exceeds the 126 MB L2; no explicit flush" % (pool_slots * 176 >> 20, w * h * 24 >> 20)},
         "mrays_per_s": mrays, "rays_per_path": (ext + shadow + probe) / paths,
         "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(w * h * 3 * 4)},
         "gpu_launches": int(launches), "roofline": roofline, "clocks": sampler.summary() if sampler else None,

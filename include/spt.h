@@ -233,7 +233,7 @@ typedef struct SptRenderDesc { /* OutputConfig (renderer/mod.rs:9-14) + PathTrac
   uint64_t seed;           /* RNG key; the stream of a path depends only on (seed, pixel, sample) */
   int32_t tile_w, tile_h;  /* screen tile size for rank interleaving (0 = 32) */
   int32_t rank, world_size;/* this process renders the tiles it owns; others stay 0 */
-  int32_t pool_size;       /* resident path slots (0 = default 2^20) */
+  int32_t pool_size;       /* resident path slots (0 = default: 2^22, fewer for small renders) */
   uint32_t flags;
 } SptRenderDesc;
 

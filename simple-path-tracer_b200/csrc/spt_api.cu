@@ -282,7 +282,9 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   cudaStream_t st = s->stream;
   const size_t n_px = (size_t)r->width * r->height;
   // ---- buffers
-  int pool_n = r->pool_size > 0 ? r->pool_size : (1 << 20);
+  // default pool: 2^22 slots (measured optimum on B200 for 1080p..4K frames), fewer for renders smaller than that
+  const unsigned long long all_samples = (unsigned long long)n_px * (unsigned long long)spp;
+  int pool_n = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 22, std::max<unsigned long long>(1ull << 16, all_samples));
   pool_n = std::max(SPT_TRAV_BLOCK, (pool_n + SPT_TRAV_BLOCK - 1) / SPT_TRAV_BLOCK * SPT_TRAV_BLOCK);
   const size_t per_slot = 4 * sizeof(float4) + sizeof(int32_t) + sizeof(uint64_t) + 3 * sizeof(uint32_t) + 3 * sizeof(float4) + SPT_NQ * sizeof(uint32_t);
   if (s->pool_n != pool_n) {
