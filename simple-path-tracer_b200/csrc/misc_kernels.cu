@@ -114,20 +114,34 @@ __global__ void __launch_bounds__(SPT_BLOCK) k_special(const DScene sc, const Re
 }
 
 // ---- generate: refill finished / empty slots from the sample cursor (render loop pt.rs:263-280 + pixel sampler + camera) ----
+// Camera-sample ordinals are reserved with ONE global atomic per block and trip (block-wide count of free slots via
+// ballot + shared memory), and handed out in slot order, so a warp's new paths are consecutive ordinals = an 8x4 pixel
+// block of primary rays.  An ordinal that falls into the padding of an edge tile leaves its slot free until the next
+// iteration.
 __global__ void __launch_bounds__(SPT_LOGIC_BLOCK) k_generate(const DScene sc, const RenderParams P) {
+  __shared__ uint32_t s_warp[SPT_LOGIC_BLOCK / 32];
+  __shared__ unsigned long long s_base;
   if (blockIdx.x == 0 && threadIdx.x < SPT_NQ) P.ctr->it.q[threadIdx.x] = 0; // the shade kernels of this iteration are done
   uint32_t n_new = 0, n_live = 0;
-  for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < P.pool.n; slot += gridDim.x * blockDim.x) {
-    if (P.pool.flags[slot] & 1u) { n_live++; continue; }
-    bool got = false;
-    uint32_t k = 0, pixel = 0;
-    unsigned long long s = warp_reserve<unsigned long long>(&P.ctr->cursor, true);
-    for (;;) {
-      if (s >= P.total_samples) break;
-      if (ordinal_to_sample(P, s, pixel, k)) { got = true; break; }
-      s = atomicAdd(&P.ctr->cursor, 1ull);
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  for (int base_slot = blockIdx.x * blockDim.x; base_slot < P.pool.n; base_slot += gridDim.x * blockDim.x) {
+    const int slot = base_slot + (int)threadIdx.x;
+    const bool in_range = slot < P.pool.n;
+    const bool dead = in_range && !(P.pool.flags[slot] & 1u);
+    if (in_range && !dead) n_live++;
+    const uint32_t m = __ballot_sync(0xffffffffu, dead);
+    if (lane == 0) s_warp[warp] = __popc(m);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t total = 0;
+      for (int w = 0; w < SPT_LOGIC_BLOCK / 32; w++) { const uint32_t c = s_warp[w]; s_warp[w] = total; total += c; }
+      s_base = total ? atomicAdd(&P.ctr->cursor, (unsigned long long)total) : 0ull;
     }
-    if (!got) continue;
+    __syncthreads();
+    const unsigned long long ord = s_base + s_warp[warp] + __popc(m & ((1u << lane) - 1u));
+    __syncthreads(); // s_warp / s_base are rewritten by the next trip
+    uint32_t k = 0, pixel = 0;
+    if (!dead || ord >= P.total_samples || !ordinal_to_sample(P, ord, pixel, k)) continue;
     PathRng rng; rng.state = rng_init(P.seed, pixel, k);
     float ox, oy, x, y;
     pixel_offset(P, pixel, k, rng, ox, oy);
@@ -143,11 +157,7 @@ __global__ void __launch_bounds__(SPT_LOGIC_BLOCK) k_generate(const DScene sc, c
     n_new++; n_live++;
   }
   warp_sum_to(&P.ctr->paths, n_new);
-  {
-    const unsigned active = __activemask();
-    const uint32_t s = __reduce_add_sync(active, n_live);
-    if (s && lane_id() == (uint32_t)(__ffs(active) - 1)) atomicAdd(&P.ctr->it.live, s);
-  }
+  warp_sum_to32(&P.ctr->it.live, n_live);
 }
 
 // ---- resolve: Film::filter_pixel for box r<=0.5 (own-pixel mean, film.rs:68-91) + color_to_rgb (film.rs:94-99) -----

@@ -53,9 +53,12 @@ SPT_D void push_shadow(const RenderParams& P, const ShadowRay& sh, uint32_t pixe
 }
 
 // ---- shade<MAT>: surface hits of one material class (pt.rs:112-193) --------------------------------------------------------------
-template <int MAT> struct ShadeCfg { static constexpr int min_blocks = 3; };
-template <> struct ShadeCfg<0> { static constexpr int min_blocks = 4; };
-template <> struct ShadeCfg<1> { static constexpr int min_blocks = 4; };
+// Resident blocks per SM the shade kernels are compiled for (register budget = 65536 / (128 * min_blocks)).
+#ifdef SPT_SHADE_MINB
+template <int MAT> struct ShadeCfg { static constexpr int min_blocks = SPT_SHADE_MINB; };
+#else
+template <int MAT> struct ShadeCfg { static constexpr int min_blocks = 4; }; // measured best of 2..6 on every config
+#endif
 
 template <int MAT, bool COUNT>
 __global__ void __launch_bounds__(SPT_BLOCK, ShadeCfg<MAT>::min_blocks) k_shade(const DScene sc, const RenderParams P) {

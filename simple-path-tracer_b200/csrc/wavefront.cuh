@@ -54,6 +54,12 @@ SPT_D void warp_sum_to(unsigned long long* dst, uint32_t v) {
   if (s && lane_id() == (uint32_t)(__ffs(active) - 1)) atomicAdd(dst, (unsigned long long)s);
 }
 
+SPT_D void warp_sum_to32(uint32_t* dst, uint32_t v) {
+  const unsigned active = __activemask();
+  const uint32_t s = __reduce_add_sync(active, v);
+  if (s && lane_id() == (uint32_t)(__ffs(active) - 1)) atomicAdd(dst, s);
+}
+
 // Camera sample ordinal -> (pixel, k).  Ordinals run tile-major, then sample-major, then 8x4 pixel blocks inside
 // the tile so that a warp holds an 8x4 block of primary rays.  Returns false for the padding of edge tiles.
 SPT_D bool ordinal_to_sample(const RenderParams& P, unsigned long long s, uint32_t& pixel, uint32_t& k) {
