@@ -246,6 +246,7 @@ def main():
                    "parallelism": f"tiles{world}", "pool_slots": pool_slots,
                    "l2_policy": "per-step working set (path pool %d MB + film %d MB) exceeds the 126 MB L2; no explicit flush" % (pool_slots * 176 >> 20, w * h * 24 >> 20)},
         "mrays_per_s": mrays, "rays_per_path": (ext + shadow + probe) / paths,
+        "shadow_rays_culled_per_path": sum(s["shadow_culled"] for s in stats) / max(1.0, sum(s["paths"] for s in stats)),
         "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(w * h * 3 * 4)},
         "gpu_launches": int(launches), "roofline": roofline, "clocks": sampler.summary() if sampler else None,
     }

@@ -240,7 +240,7 @@ typedef struct SptRenderDesc { /* OutputConfig (renderer/mod.rs:9-14) + PathTrac
 typedef struct SptStats {
   uint64_t paths;          /* camera samples traced by this rank */
   uint64_t ext_rays;       /* closest-hit rays (pt.rs:50) */
-  uint64_t shadow_rays;    /* any-hit rays (pt.rs:81,169) */
+  uint64_t shadow_rays;    /* any-hit rays actually traced (pt.rs:81,169) */
   uint64_t probe_rays;     /* BSSRDF probes (substrate.rs:290) */
   uint64_t nodes_visited, tris_tested, insts_visited; /* only with SPT_RENDER_COUNT_TRAVERSAL */
   uint64_t nonfinite;      /* contributions dropped because they were NaN/Inf */
@@ -248,6 +248,9 @@ typedef struct SptStats {
   uint64_t kernel_launches;
   double seconds_total;    /* device time of the whole render (CUDA events) */
   double seconds_stage[6]; /* generate, extend, shade, connect, resolve, other */
+  uint64_t shadow_culled;  /* NEE samples whose contribution was exactly zero (light behind the surface, black emitter):
+                              the reference still calls intersect_test for them (pt.rs:169); this core skips the
+                              any-hit ray because its result is multiplied by zero.  Not counted in shadow_rays. */
 } SptStats;
 
 typedef struct SptSceneInfo {

@@ -34,7 +34,7 @@ __global__ void __launch_bounds__(SPT_LOGIC_BLOCK) k_logic(const DScene sc, cons
 // A path that leaves its medium is handed on to the material queue of the surface it left through, to be shaded in
 // this same iteration with the cached hit (Q21: the reference re-traces the same ray and finds the same hit).
 __global__ void __launch_bounds__(SPT_BLOCK) k_special(const DScene sc, const RenderParams P) {
-  uint32_t nonfinite = 0;
+  uint32_t nonfinite = 0, n_culled = 0;
   const uint32_t n = P.ctr->it.q[SPT_Q_SPECIAL];
   const uint32_t* queue = P.queue + (size_t)SPT_Q_SPECIAL * P.pool.n;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(SPT_BLOCK) k_special(const DScene sc, const Re
         terminate = true;
       } else to_surface = true;
     }
-    push_shadow(P, sh, s.pixel);
+    push_shadow(P, sh, s.pixel, n_culled);
     if (to_surface) { // write back what the medium changed, then queue for surface shading
       P.pool.thr[slot] = make_float4(s.thr.x, s.thr.y, s.thr.z, s.last_pdf);
       P.pool.rng[slot] = s.rng.state;
@@ -111,6 +111,7 @@ __global__ void __launch_bounds__(SPT_BLOCK) k_special(const DScene sc, const Re
     } else finish_bounce(P, slot, s, terminate);
   }
   warp_sum_to(&P.ctr->nonfinite, nonfinite);
+  warp_sum_to(&P.ctr->shadow_culled, n_culled);
 }
 
 // ---- generate: refill finished / empty slots from the sample cursor (render loop pt.rs:263-280 + pixel sampler + camera) ----

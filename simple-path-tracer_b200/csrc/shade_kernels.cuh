@@ -43,9 +43,14 @@ SPT_D void finish_bounce(const RenderParams& P, int slot, PathRegs& s, bool term
   P.pool.flags[slot] = 1u | ((uint32_t)s.depth << 8) | ((uint32_t)(s.medium + 1) << 16);
 }
 // Shadow-ray emission into the compacted queue, one atomic per warp.
-SPT_D void push_shadow(const RenderParams& P, const ShadowRay& sh, uint32_t pixel) {
-  const uint32_t qi = warp_reserve<uint32_t>(&P.ctr->it.sq, sh.emit);
-  if (sh.emit) {
+// A sample whose contribution is exactly zero (light behind the surface, BxDF zero across the horizon, black emitter)
+// is not queued: its any-hit result would be multiplied by zero.  NaN contributions are kept (they must be counted).
+SPT_D void push_shadow(const RenderParams& P, const ShadowRay& sh, uint32_t pixel, uint32_t& n_culled) {
+  const bool zero = sh.c.x == 0.0f && sh.c.y == 0.0f && sh.c.z == 0.0f;
+  const bool emit = sh.emit && !zero;
+  if (sh.emit && zero) n_culled++;
+  const uint32_t qi = warp_reserve<uint32_t>(&P.ctr->it.sq, emit);
+  if (emit) {
     P.sq.o[qi] = make_float4(sh.o.x, sh.o.y, sh.o.z, sh.tmin);
     P.sq.d[qi] = make_float4(sh.d.x, sh.d.y, sh.d.z, sh.tmax);
     P.sq.c[qi] = make_float4(sh.c.x, sh.c.y, sh.c.z, __uint_as_float(pixel));
@@ -64,7 +69,7 @@ template <int MAT, bool COUNT>
 __global__ void __launch_bounds__(SPT_BLOCK, ShadeCfg<MAT>::min_blocks) k_shade(const DScene sc, const RenderParams P) {
   constexpr bool PROBE = MAT < 0 || MAT == 7; // the BSSRDF probe ray needs the traversal stack
   __shared__ uint2 s_stack[PROBE ? SPT_SSTACK : 1][PROBE ? SPT_TRAV_BLOCK : 1];
-  uint32_t nonfinite = 0, n_probe = 0;
+  uint32_t nonfinite = 0, n_probe = 0, n_culled = 0;
   TravCounters tc = {0, 0, 0};
   constexpr int QI = MAT < 0 ? SPT_Q_GENERIC : MAT;
   const uint32_t n = P.ctr->it.q[QI];
@@ -170,10 +175,11 @@ __global__ void __launch_bounds__(SPT_BLOCK, ShadeCfg<MAT>::min_blocks) k_shade(
       if (!(bs.dir == DIR_REFLECT ? hd >= 0.f : hd <= 0.f)) terminate = true;
       else if (dot3(wi_world, g.n) < 0.f) s.medium = sf.double_sided ? -1 : sf.inside_medium; // pt.rs:190-192, surface.rs:105-111
     }
-    push_shadow(P, sh, s.pixel);
+    push_shadow(P, sh, s.pixel, n_culled);
     finish_bounce(P, slot, s, terminate);
   }
   warp_sum_to(&P.ctr->nonfinite, nonfinite);
+  warp_sum_to(&P.ctr->shadow_culled, n_culled);
   if (PROBE) warp_sum_to(&P.ctr->probe_rays, n_probe);
   if (COUNT && PROBE) { warp_sum_to(&P.ctr->nodes, tc.nodes); warp_sum_to(&P.ctr->tris, tc.tris); warp_sum_to(&P.ctr->insts, tc.insts); }
 }

@@ -30,7 +30,7 @@ struct IterCounters { // per-iteration device counters; each is zeroed by a kern
 };
 struct DevCounters { // device-side totals of one render
   unsigned long long cursor;      // next camera-sample ordinal
-  unsigned long long paths, ext_rays, shadow_rays, probe_rays, nonfinite, nodes, tris, insts;
+  unsigned long long paths, ext_rays, shadow_rays, probe_rays, nonfinite, nodes, tris, insts, shadow_culled;
   IterCounters it;
 };
 struct RenderParams {

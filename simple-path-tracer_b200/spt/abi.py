@@ -114,7 +114,8 @@ class Stats(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("ext_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("probe_rays", C.c_uint64), ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
                 ("insts_visited", C.c_uint64), ("nonfinite", C.c_uint64), ("iterations", C.c_uint64),
-                ("kernel_launches", C.c_uint64), ("seconds_total", C.c_double), ("seconds_stage", C.c_double * 6)]
+                ("kernel_launches", C.c_uint64), ("seconds_total", C.c_double), ("seconds_stage", C.c_double * 6),
+                ("shadow_culled", C.c_uint64)]
 
     def as_dict(self):
         d = {k: getattr(self, k) for k, _ in self._fields_ if k != "seconds_stage"}

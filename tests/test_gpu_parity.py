@@ -87,7 +87,8 @@ def test_paired_render_matches_oracle(scene_pair, name, sampler, div):
     rel = (np.abs(gi - oi) / (np.abs(oi) + 1e-3))[fin]
     frac = float((rel.max(-1) < 1e-3).mean())
     assert frac >= 0.995, (name, frac)
-    assert abs(gst["shadow_rays"] / ost["shadow_rays"] - 1) < 2e-3
+    # the reference calls intersect_test for every NEE sample; the CUDA core skips those with an exactly zero contribution
+    assert abs((gst["shadow_rays"] + gst["shadow_culled"]) / ost["shadow_rays"] - 1) < 2e-3
     assert abs(float(gi[fin].mean()) / float(oi[fin].mean()) - 1) < 0.05
 
 

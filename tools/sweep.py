@@ -41,6 +41,6 @@ for item in args.items:
                           "mpaths_s_untimed": plain["paths"] / plain["seconds_total"] / 1e6,
                           "mrays_s": rays / best["seconds_total"] / 1e6, "iters": best["iterations"], "launches": best["kernel_launches"],
                           "sec": best["seconds_total"], "stage": [round(x, 5) for x in best["seconds_stage"]],
-                          "ext": best["ext_rays"], "shadow": best["shadow_rays"], "probe": best["probe_rays"],
+                          "ext": best["ext_rays"], "shadow": best["shadow_rays"], "probe": best["probe_rays"], "culled": best["shadow_culled"],
                           "mean": float(fb.mean().item())}), flush=True)
     sc.close()
