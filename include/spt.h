@@ -251,6 +251,8 @@ typedef struct SptStats {
   uint64_t shadow_culled;  /* NEE samples whose contribution was exactly zero (light behind the surface, black emitter):
                               the reference still calls intersect_test for them (pt.rs:169); this core skips the
                               any-hit ray because its result is multiplied by zero.  Not counted in shadow_rays. */
+  uint64_t trav_profile[10]; /* only with SPT_RENDER_COUNT_TRAVERSAL: lane-rounds with a ray, lanes active in the pop /
+                                node / instance / triangle stage, then warp-rounds total and warp-rounds that ran each stage */
 } SptStats;
 
 typedef struct SptSceneInfo {

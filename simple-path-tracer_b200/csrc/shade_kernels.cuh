@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(SPT_BLOCK, ShadeCfg<MAT>::min_blocks) k_shade(
   constexpr bool PROBE = MAT < 0 || MAT == 7; // the BSSRDF probe ray needs the traversal stack
   __shared__ uint2 s_stack[PROBE ? SPT_SSTACK : 1][PROBE ? SPT_TRAV_BLOCK : 1];
   uint32_t nonfinite = 0, n_probe = 0, n_culled = 0;
-  TravCounters tc = {0, 0, 0};
+  TravCounters tc = {};
   constexpr int QI = MAT < 0 ? SPT_Q_GENERIC : MAT;
   const uint32_t n = P.ctr->it.q[QI];
   const uint32_t* queue = P.queue + (size_t)QI * P.pool.n;

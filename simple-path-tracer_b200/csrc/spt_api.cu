@@ -400,6 +400,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
     const DevCounters& c = *s->h_ctr;
     stats->paths = c.paths; stats->ext_rays = c.ext_rays; stats->shadow_rays = c.shadow_rays; stats->probe_rays = c.probe_rays;
     stats->nodes_visited = c.nodes; stats->tris_tested = c.tris; stats->insts_visited = c.insts; stats->nonfinite = c.nonfinite; stats->shadow_culled = c.shadow_culled;
+    for (int i = 0; i < 10; i++) stats->trav_profile[i] = c.trav_profile[i];
     stats->iterations = iters; stats->kernel_launches = launches; stats->seconds_total = ms * 1e-3;
     for (int i = 0; i < 6; i++) stats->seconds_stage[i] = stage[i];
   }

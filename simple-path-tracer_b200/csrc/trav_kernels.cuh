@@ -4,6 +4,13 @@
 
 #define SPT_BLOCK SPT_TRAV_BLOCK
 
+SPT_D void flush_trav_counters(DevCounters* ctr, const TravCounters& tc) {
+  warp_sum_to(&ctr->nodes, tc.nodes); warp_sum_to(&ctr->tris, tc.tris); warp_sum_to(&ctr->insts, tc.insts);
+  const uint32_t v[10] = {tc.busy, tc.pop, tc.node, tc.inst, tc.tri, tc.w_rounds, tc.w_pop, tc.w_node, tc.w_inst, tc.w_tri};
+#pragma unroll
+  for (int i = 0; i < 10; i++) warp_sum_to(&ctr->trav_profile[i], v[i]);
+}
+
 // ---- ray sources of the persistent traversal driver -------------------------------------------------------------
 struct ExtendSrc { // every live path of the pool: closest hit (pt.rs:49-50)
   const RenderParams& P;
@@ -37,22 +44,22 @@ struct ConnectSrc { // the queued shadow rays: any hit (pt.rs:81, :169); unocclu
 
 template <bool COUNT>
 __global__ void __launch_bounds__(SPT_BLOCK) k_extend(const DScene sc, const RenderParams P) {
-  TravCounters tc = {0, 0, 0};
+  TravCounters tc = {};
   if (blockIdx.x == 0 && threadIdx.x == 0) { P.ctr->it.sq = 0; P.ctr->it.next_con = 0; } // connect of this iteration is done
   ExtendSrc src{P, 0};
   trace_persistent<false, COUNT>(sc, src, &P.ctr->it.next_ext, tc);
   warp_sum_to(&P.ctr->ext_rays, src.n_rays);
-  if (COUNT) { warp_sum_to(&P.ctr->nodes, tc.nodes); warp_sum_to(&P.ctr->tris, tc.tris); warp_sum_to(&P.ctr->insts, tc.insts); }
+  if (COUNT) flush_trav_counters(P.ctr, tc);
 }
 
 template <bool COUNT>
 __global__ void __launch_bounds__(SPT_BLOCK) k_connect(const DScene sc, const RenderParams P) {
-  TravCounters tc = {0, 0, 0};
+  TravCounters tc = {};
   ConnectSrc src{P, P.ctr->it.sq, 0};
   trace_persistent<true, COUNT>(sc, src, &P.ctr->it.next_con, tc);
   if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&P.ctr->shadow_rays, (unsigned long long)src.n);
   warp_sum_to(&P.ctr->nonfinite, src.nonfinite);
-  if (COUNT) { warp_sum_to(&P.ctr->nodes, tc.nodes); warp_sum_to(&P.ctr->tris, tc.tris); warp_sum_to(&P.ctr->insts, tc.insts); }
+  if (COUNT) flush_trav_counters(P.ctr, tc);
 }
 
 // ---- seam B2 on caller-supplied ray batches -------------------------------------------------------------------
@@ -87,8 +94,8 @@ struct BatchSrc {
 template <bool ANY, bool COUNT>
 __global__ void __launch_bounds__(SPT_BLOCK) k_batch(const DScene sc, const float4* __restrict__ rays, uint32_t n, HitIO* __restrict__ hits,
                                                      uint8_t* __restrict__ occ, uint32_t* next, DevCounters* ctr) {
-  TravCounters tc = {0, 0, 0};
+  TravCounters tc = {};
   BatchSrc src{sc, rays, n, hits, occ};
   trace_persistent<ANY, COUNT>(sc, src, next, tc);
-  if (COUNT && ctr) { warp_sum_to(&ctr->nodes, tc.nodes); warp_sum_to(&ctr->tris, tc.tris); warp_sum_to(&ctr->insts, tc.insts); }
+  if (COUNT && ctr) flush_trav_counters(ctr, tc);
 }

@@ -25,7 +25,12 @@ struct HitRec {
   int prim, inst; // prim: triangle id inside its mesh (file order) or 0 for a sphere; inst: instance id, -1 = miss
   int tri;        // global index of the triangle in `tris` / `shade_tris` (leaf order), -1 for a sphere
 };
-struct TravCounters { uint32_t nodes, tris, insts; };
+struct TravCounters { // only maintained by the COUNT instantiations
+  uint32_t nodes, tris, insts;
+  // warp-round profile of the persistent driver (per lane): rounds spent with a ray, and lanes active in each stage;
+  // lane 0 also counts the rounds of its warp and how many rounds executed each stage at all
+  uint32_t busy, pop, node, inst, tri, w_rounds, w_pop, w_node, w_inst, w_tri;
+};
 
 #define SPT_SSTACK 16       // stack entries per thread in shared memory
 #define SPT_LSTACK 32       // overflow entries in local memory (untouched unless a ray goes deeper than SPT_SSTACK)
@@ -341,21 +346,36 @@ SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCoun
       w_next += take;
     }
     bool fin = false;
+    if (COUNT) { cnt.busy += has ? 1u : 0u; if (lane == 0) cnt.w_rounds++; }
     // ---- pop: nothing pending -> leave the BLAS / next stack entry / ray finished
-    if (has && !trav_has_node(T) && !trav_has_leaf(T)) fin = trav_pop(T, st);
+    {
+      const bool p = has && !trav_has_node(T) && !trav_has_leaf(T);
+      if (COUNT) { const uint32_t m = __ballot_sync(FULL, p); cnt.pop += p ? 1u : 0u; if (lane == 0 && m) cnt.w_pop++; }
+      if (p) fin = trav_pop(T, st);
+    }
 #if SPT_STAGE_ORDER == 1
     if (has && !fin && trav_has_leaf(T) && T.cur_inst < 0) fin = trav_inst<ANY, COUNT>(sc, T, st, cnt);
 #endif
     // ---- node step
-    if (has && !fin && trav_has_node(T) && !trav_has_leaf(T)) trav_node<COUNT>(sc, T, st, cnt);
+    {
+      const bool p = has && !fin && trav_has_node(T) && !trav_has_leaf(T);
+      if (COUNT) { const uint32_t m = __ballot_sync(FULL, p); cnt.node += p ? 1u : 0u; if (lane == 0 && m) cnt.w_node++; }
+      if (p) trav_node<COUNT>(sc, T, st, cnt);
+    }
     // ---- instance visit (TLAS leaf)
 #pragma unroll
-    for (int k = 0; k < SPT_INST_PER_ROUND; k++)
-      if (has && !fin && trav_has_leaf(T) && T.cur_inst < 0) fin = trav_inst<ANY, COUNT>(sc, T, st, cnt);
+    for (int k = 0; k < SPT_INST_PER_ROUND; k++) {
+      const bool p = has && !fin && trav_has_leaf(T) && T.cur_inst < 0;
+      if (COUNT) { const uint32_t m = __ballot_sync(FULL, p); cnt.inst += p ? 1u : 0u; if (lane == 0 && m) cnt.w_inst++; }
+      if (p) fin = trav_inst<ANY, COUNT>(sc, T, st, cnt);
+    }
     // ---- triangle tests (BLAS leaf / small mesh)
 #pragma unroll
-    for (int k = 0; k < SPT_TRI_PER_ROUND; k++)
-      if (has && !fin && trav_has_leaf(T) && T.cur_inst >= 0) fin = trav_tri<ANY, COUNT>(sc, T, cnt);
+    for (int k = 0; k < SPT_TRI_PER_ROUND; k++) {
+      const bool p = has && !fin && trav_has_leaf(T) && T.cur_inst >= 0;
+      if (COUNT) { const uint32_t m = __ballot_sync(FULL, p); cnt.tri += p ? 1u : 0u; if (lane == 0 && m) cnt.w_tri++; }
+      if (p) fin = trav_tri<ANY, COUNT>(sc, T, cnt);
+    }
     if (fin) { src.store(idx, T.hit); has = false; }
   }
 }

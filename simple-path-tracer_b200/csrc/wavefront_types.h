@@ -31,6 +31,7 @@ struct IterCounters { // per-iteration device counters; each is zeroed by a kern
 struct DevCounters { // device-side totals of one render
   unsigned long long cursor;      // next camera-sample ordinal
   unsigned long long paths, ext_rays, shadow_rays, probe_rays, nonfinite, nodes, tris, insts, shadow_culled;
+  unsigned long long trav_profile[10]; // COUNT builds: see TravCounters
   IterCounters it;
 };
 struct RenderParams {

@@ -115,10 +115,11 @@ class Stats(C.Structure):
                 ("probe_rays", C.c_uint64), ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
                 ("insts_visited", C.c_uint64), ("nonfinite", C.c_uint64), ("iterations", C.c_uint64),
                 ("kernel_launches", C.c_uint64), ("seconds_total", C.c_double), ("seconds_stage", C.c_double * 6),
-                ("shadow_culled", C.c_uint64)]
+                ("shadow_culled", C.c_uint64), ("trav_profile", C.c_uint64 * 10)]
 
     def as_dict(self):
-        d = {k: getattr(self, k) for k, _ in self._fields_ if k != "seconds_stage"}
+        d = {k: getattr(self, k) for k, _ in self._fields_ if k not in ("seconds_stage", "trav_profile")}
+        d["trav_profile"] = list(self.trav_profile)
         d["seconds_stage"] = list(self.seconds_stage)
         return d
 
