@@ -46,14 +46,14 @@ SPT_D uint32_t bfind_u32(uint32_t x) { uint32_t v; asm("bfind.u32 %0, %1;" : "=r
 SPT_D float4 ldg4(const float4* p) { return __ldg(p); }
 
 struct RaySetup { float3 o, d, idir; uint32_t octinv4; };
+SPT_D float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; } // MUFU.RCP, 1 ulp
+// |d| clamped away from zero (keeps its sign) so that 1/d stays finite; 1-ulp reciprocal: only the conservative box
+// tests use idir.  Octant from the sign bits.
+SPT_D float clamp_dir(float d) { return __uint_as_float((__float_as_uint(fmaxf(fabsf(d), 1e-18f)) & 0x7fffffffu) | (__float_as_uint(d) & 0x80000000u)); }
 SPT_D void ray_setup(RaySetup& r, float3 o, float3 d) {
   r.o = o; r.d = d;
-  const float eps = 1e-18f;
-  float dx = fabsf(d.x) < eps ? copysignf(eps, d.x) : d.x;
-  float dy = fabsf(d.y) < eps ? copysignf(eps, d.y) : d.y;
-  float dz = fabsf(d.z) < eps ? copysignf(eps, d.z) : d.z;
-  r.idir = mk3(__fdividef(1.0f, dx), __fdividef(1.0f, dy), __fdividef(1.0f, dz)); // approximate (1 ulp): only the conservative box tests use it
-  uint32_t oct = (d.x < 0.f ? 4u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 1u : 0u);
+  r.idir = mk3(rcp_approx(clamp_dir(d.x)), rcp_approx(clamp_dir(d.y)), rcp_approx(clamp_dir(d.z)));
+  const uint32_t oct = ((__float_as_uint(d.x) >> 31) << 2) | ((__float_as_uint(d.y) >> 31) << 1) | (__float_as_uint(d.z) >> 31);
   r.octinv4 = (7u - oct) * 0x01010101u;
 }
 
