@@ -102,8 +102,8 @@ __global__ void __launch_bounds__(SPT_BLOCK) k_special(const DScene sc, const Re
     }
     push_shadow(P, sh, s.pixel, n_culled);
     if (to_surface) { // write back what the medium changed, then queue for surface shading
-      P.pool.thr[slot] = make_float4(s.thr.x, s.thr.y, s.thr.z, s.last_pdf);
-      P.pool.rng[slot] = s.rng.state;
+      P.pool.rec[slot].thr = make_float4(s.thr.x, s.thr.y, s.thr.z, s.last_pdf);
+      P.pool.rec[slot].aux = make_uint4((uint32_t)s.rng.state, (uint32_t)(s.rng.state >> 32), s.pixel, s.sample);
       P.pool.flags[slot] = 1u | ((uint32_t)s.depth << 8);
       const int cls = P.sort_materials ? (int)sc.inst_mat[hit.inst] : SPT_Q_GENERIC;
       const uint32_t qi = atomicAdd(&P.ctr->it.q[cls], 1u);
@@ -148,12 +148,11 @@ __global__ void __launch_bounds__(SPT_LOGIC_BLOCK) k_generate(const DScene sc, c
     pixel_offset(P, pixel, k, rng, ox, oy);
     film_xy(P, pixel, ox, oy, x, y);
     const float3 rd = camera_dir(sc.camera, x, y);
-    P.pool.ray_o[slot] = make_float4(sc.camera.eye[0], sc.camera.eye[1], sc.camera.eye[2], 1e-4f);
-    P.pool.ray_d[slot] = make_float4(rd.x, rd.y, rd.z, 0.f);
-    P.pool.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
-    P.pool.rng[slot] = rng.state;
-    P.pool.pixel[slot] = pixel;
-    P.pool.sample[slot] = k;
+    PathRec* rec = P.pool.rec + slot;
+    rec->ray_o = make_float4(sc.camera.eye[0], sc.camera.eye[1], sc.camera.eye[2], 1e-4f);
+    rec->ray_d = make_float4(rd.x, rd.y, rd.z, 0.f);
+    rec->thr = make_float4(1.f, 1.f, 1.f, 0.f);
+    rec->aux = make_uint4((uint32_t)rng.state, (uint32_t)(rng.state >> 32), pixel, k);
     P.pool.flags[slot] = 1u;
     n_new++; n_live++;
   }

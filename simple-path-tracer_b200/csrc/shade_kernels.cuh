@@ -9,18 +9,20 @@ struct PathRegs {
   float3 ro, rd, thr;
   float rtmin, last_pdf;
   PathRng rng;
-  uint32_t pixel;
+  uint32_t pixel, sample;
   int depth, medium;
 };
 struct ShadowRay { float3 o, d, c; float tmin, tmax; bool emit; };
 
 SPT_D void load_path(const RenderParams& P, int slot, uint32_t flags, PathRegs& s, HitRec& hit) {
-  const float4 o4 = P.pool.ray_o[slot], d4 = P.pool.ray_d[slot], h4 = P.pool.hit[slot], t4 = P.pool.thr[slot];
+  const PathRec* rec = P.pool.rec + slot;
+  const float4 o4 = rec->ray_o, d4 = rec->ray_d, t4 = rec->thr, h4 = P.pool.hit[slot];
+  const uint4 aux = rec->aux;
   s.ro = mk3(o4); s.rd = mk3(d4); s.rtmin = o4.w;
   hit.t = h4.x; hit.u = h4.y; hit.v = h4.z; hit.tri = __float_as_int(h4.w); hit.prim = 0; hit.inst = P.pool.hit_inst[slot];
   s.thr = mk3(t4); s.last_pdf = t4.w;
-  s.rng.state = P.pool.rng[slot];
-  s.pixel = P.pool.pixel[slot];
+  s.rng.state = (uint64_t)aux.x | ((uint64_t)aux.y << 32);
+  s.pixel = aux.z; s.sample = aux.w;
   s.depth = (int)((flags >> 8) & 0xffu);
   s.medium = (int)(flags >> 16) - 1;
 }
@@ -36,10 +38,11 @@ SPT_D void finish_bounce(const RenderParams& P, int slot, PathRegs& s, bool term
     }
   }
   if (terminate) { P.pool.flags[slot] = 0u; return; }
-  P.pool.ray_o[slot] = make_float4(s.ro.x, s.ro.y, s.ro.z, s.rtmin);
-  P.pool.ray_d[slot] = make_float4(s.rd.x, s.rd.y, s.rd.z, 0.f);
-  P.pool.thr[slot] = make_float4(s.thr.x, s.thr.y, s.thr.z, s.last_pdf);
-  P.pool.rng[slot] = s.rng.state;
+  PathRec* rec = P.pool.rec + slot; // the whole record: two full sectors, no partial-sector fills
+  rec->ray_o = make_float4(s.ro.x, s.ro.y, s.ro.z, s.rtmin);
+  rec->ray_d = make_float4(s.rd.x, s.rd.y, s.rd.z, 0.f);
+  rec->thr = make_float4(s.thr.x, s.thr.y, s.thr.z, s.last_pdf);
+  rec->aux = make_uint4((uint32_t)s.rng.state, (uint32_t)(s.rng.state >> 32), s.pixel, s.sample);
   P.pool.flags[slot] = 1u | ((uint32_t)s.depth << 8) | ((uint32_t)(s.medium + 1) << 16);
 }
 // Shadow-ray emission into the compacted queue, one atomic per warp.
@@ -85,7 +88,7 @@ __global__ void __launch_bounds__(SPT_BLOCK, ShadeCfg<MAT>::min_blocks) k_shade(
     HitGeom g;
     load_hit(sc, s.ro, s.rd, hit, g);
     if (s.depth == 0 && sc.has_image_tex) { // ray differentials exist only for camera rays (Q18)
-      const uint32_t k = P.pool.sample[slot];
+      const uint32_t k = s.sample;
       PathRng r2; r2.state = rng_init(P.seed, s.pixel, k);
       float ox, oy, x, y; pixel_offset(P, s.pixel, k, r2, ox, oy); film_xy(P, s.pixel, ox, oy, x, y);
       const float aspect = (float)P.width / (float)P.height, ssi = 1.0f / sqrtf((float)P.spp);

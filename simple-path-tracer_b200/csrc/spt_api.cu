@@ -286,7 +286,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   const unsigned long long all_samples = (unsigned long long)n_px * (unsigned long long)spp;
   int pool_n = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 22, std::max<unsigned long long>(1ull << 16, all_samples));
   pool_n = std::max(SPT_TRAV_BLOCK, (pool_n + SPT_TRAV_BLOCK - 1) / SPT_TRAV_BLOCK * SPT_TRAV_BLOCK);
-  const size_t per_slot = 4 * sizeof(float4) + sizeof(int32_t) + sizeof(uint64_t) + 3 * sizeof(uint32_t) + 3 * sizeof(float4) + SPT_NQ * sizeof(uint32_t);
+  const size_t per_slot = sizeof(PathRec) + sizeof(float4) + 3 * sizeof(float4) + sizeof(int32_t) + sizeof(uint32_t) + SPT_NQ * sizeof(uint32_t);
   if (s->pool_n != pool_n) {
     cudaFree(s->pool_mem); s->pool_mem = nullptr; s->pool_n = 0;
     CU(cudaMalloc(&s->pool_mem, per_slot * (size_t)pool_n));
@@ -296,17 +296,12 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   RenderParams P; memset(&P, 0, sizeof(P));
   {
     char* p = (char*)s->pool_mem; const size_t N = (size_t)pool_n;
-    P.pool.ray_o = (float4*)p; p += N * sizeof(float4);
-    P.pool.ray_d = (float4*)p; p += N * sizeof(float4);
+    P.pool.rec = (PathRec*)p; p += N * sizeof(PathRec);
     P.pool.hit = (float4*)p; p += N * sizeof(float4);
-    P.pool.thr = (float4*)p; p += N * sizeof(float4);
     P.sq.o = (float4*)p; p += N * sizeof(float4);
     P.sq.d = (float4*)p; p += N * sizeof(float4);
     P.sq.c = (float4*)p; p += N * sizeof(float4);
-    P.pool.rng = (uint64_t*)p; p += N * sizeof(uint64_t);
     P.pool.hit_inst = (int32_t*)p; p += N * sizeof(int32_t);
-    P.pool.pixel = (uint32_t*)p; p += N * sizeof(uint32_t);
-    P.pool.sample = (uint32_t*)p; p += N * sizeof(uint32_t);
     P.pool.flags = (uint32_t*)p; p += N * sizeof(uint32_t);
     P.queue = (uint32_t*)p; p += N * SPT_NQ * sizeof(uint32_t);
     P.pool.n = pool_n;

@@ -18,7 +18,7 @@ struct ExtendSrc { // every live path of the pool: closest hit (pt.rs:49-50)
   SPT_D uint32_t total() const { return (uint32_t)P.pool.n; }
   SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
     if (!(P.pool.flags[i] & 1u)) return false;
-    const float4 o4 = P.pool.ray_o[i], d4 = P.pool.ray_d[i];
+    const float4 o4 = P.pool.rec[i].ray_o, d4 = P.pool.rec[i].ray_d;
     o = mk3(o4); d = mk3(d4); tmin = o4.w; tmax = FLT_MAX; // Intersection::default, intersection.rs:86-102
     n_rays++;
     return true;

@@ -7,16 +7,19 @@
 #define SPT_Q_SPECIAL 8
 #define SPT_Q_GENERIC 9
 
-struct PathPool { // SoA over `n` slots
-  float4* ray_o;    // origin.xyz, t_min
-  float4* ray_d;    // direction.xyz, -
-  float4* hit;      // t, u, v, global triangle index (int bits; -1 = sphere)
+// Per-path state written by shade / generate: ONE 64-byte record per slot (two full 32-byte sectors), because the shade
+// kernels visit slots in queue order (a gather): with separate arrays every 16-byte field cost its own half-used sector.
+struct __align__(16) PathRec {
+  float4 ray_o;   // origin.xyz, t_min            } sector 0: all that k_extend reads
+  float4 ray_d;   // direction.xyz, -             }
+  float4 thr;     // throughput.rgb, last_sample_pdf
+  uint4 aux;      // rng state (lo, hi), pixel index j*W+i, sample index k within the pixel
+};
+struct PathPool { // `n` slots
+  PathRec* rec;
+  float4* hit;      // t, u, v, global triangle index (int bits; -1 = sphere)   written by k_extend
   int32_t* hit_inst;
-  float4* thr;      // throughput.rgb, last_sample_pdf
-  uint64_t* rng;
-  uint32_t* pixel;  // pixel index j*W+i
-  uint32_t* sample; // sample index k within the pixel
-  uint32_t* flags;  // bit0 alive | depth << 8 | (medium+1) << 16
+  uint32_t* flags;  // bit0 alive | depth << 8 | (medium+1) << 16  (dense passes read only this)
   int32_t n;
 };
 struct ShadowQueue { float4* o; float4* d; float4* c; }; // o.xyz,tmin | d.xyz,tmax | contrib.rgb,pixel
