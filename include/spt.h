@@ -220,7 +220,8 @@ typedef struct SptBxdfResult {
 
 #define SPT_RENDER_COUNT_TRAVERSAL 1u /* fill nodes_visited/tris_tested/insts_visited (slower build) */
 #define SPT_RENDER_NO_SORT 2u         /* disable material binning of the shade stage (for A/B timing) */
-#define SPT_RENDER_TIME_STAGES 4u     /* fill seconds_stage[] from CUDA events around every kernel launch */
+#define SPT_RENDER_TIME_STAGES 4u     /* fill seconds_stage[] from CUDA events around every kernel launch (implies SERIAL) */
+#define SPT_RENDER_SERIAL 8u          /* issue every kernel on one stream (default: independent kernels of an iteration overlap) */
 
 typedef struct SptRenderDesc { /* OutputConfig (renderer/mod.rs:9-14) + PathTracer fields (pt.rs:24-28) */
   int32_t camera_index;

@@ -10,7 +10,7 @@
 __global__ void __launch_bounds__(SPT_LOGIC_BLOCK) k_logic(const DScene sc, const RenderParams P) {
   __shared__ uint32_t s_cnt[SPT_NQ], s_base[SPT_NQ];
   if (threadIdx.x < SPT_NQ) s_cnt[threadIdx.x] = 0;
-  if (blockIdx.x == 0 && threadIdx.x == 0) { P.ctr->it.live = 0; P.ctr->it.next_ext = 0; }
+  if (blockIdx.x == 0 && threadIdx.x == 0) { P.ctr->it.live = 0; P.ctr->it.next_ext = 0; P.ctr->it.sq = 0; P.ctr->it.next_con = 0; } // connect + extend of the last iteration are done
   __syncthreads();
   const int slot = blockIdx.x * blockDim.x + threadIdx.x;
   int cls = -1; uint32_t rank = 0;

@@ -43,7 +43,9 @@ struct SptScene {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[2] = {nullptr, nullptr};
   cudaEvent_t sev[4] = {nullptr, nullptr, nullptr, nullptr}; // per-stage timing (SPT_RENDER_TIME_STAGES)
-  int occ_ext = 0, occ_con = 0, occ_bat = 0; // resident blocks per SM of the persistent kernels (occupancy API)
+  int occ_ext = 0, occ_con = 0, occ_bat = 0;
+  cudaStream_t aux[3] = {nullptr, nullptr, nullptr};         // [0],[1]: shade kernels of other material classes, [2]: connect
+  cudaEvent_t ev_fork = nullptr, ev_shaded = nullptr, ev_con = nullptr, ev_join[2] = {nullptr, nullptr}; // resident blocks per SM of the persistent kernels (occupancy API)
 };
 
 namespace {
@@ -134,6 +136,10 @@ int32_t spt_scene_create(SptContext* ctx, const SptSceneDesc* desc, SptScene** o
   CU(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
   CU(cudaEventCreate(&s->ev[0])); CU(cudaEventCreate(&s->ev[1]));
   for (int i = 0; i < 4; i++) CU(cudaEventCreate(&s->sev[i]));
+  for (int i = 0; i < 3; i++) CU(cudaStreamCreateWithFlags(&s->aux[i], cudaStreamNonBlocking));
+  CU(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming)); CU(cudaEventCreateWithFlags(&s->ev_shaded, cudaEventDisableTiming));
+  CU(cudaEventCreateWithFlags(&s->ev_con, cudaEventDisableTiming));
+  for (int i = 0; i < 2; i++) CU(cudaEventCreateWithFlags(&s->ev_join[i], cudaEventDisableTiming));
   CU(cudaMalloc(&s->ctr, sizeof(DevCounters))); CU(cudaMalloc(&s->batch_next, sizeof(uint32_t)));
   CU(cudaMallocHost(&s->h_ctr, sizeof(DevCounters)));
   *out = s;
@@ -169,6 +175,11 @@ int32_t spt_scene_destroy(SptScene* s) {
   if (s->ev[0]) cudaEventDestroy(s->ev[0]);
   if (s->ev[1]) cudaEventDestroy(s->ev[1]);
   for (int i = 0; i < 4; i++) if (s->sev[i]) cudaEventDestroy(s->sev[i]);
+  for (int i = 0; i < 3; i++) if (s->aux[i]) cudaStreamDestroy(s->aux[i]);
+  if (s->ev_fork) cudaEventDestroy(s->ev_fork);
+  if (s->ev_shaded) cudaEventDestroy(s->ev_shaded);
+  if (s->ev_con) cudaEventDestroy(s->ev_con);
+  for (int i = 0; i < 2; i++) if (s->ev_join[i]) cudaEventDestroy(s->ev_join[i]);
   if (s->stream) cudaStreamDestroy(s->stream);
   delete s;
   return SPT_OK;
@@ -341,16 +352,40 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   double stage[6] = {0, 0, 0, 0, 0, 0}; // generate (inside shade), extend, shade (logic..generate), connect, resolve, other
   const uint32_t mats = P.sort_materials ? ds.mat_mask : 0u;
   const bool special = ds.has_medium || ds.env_tex != nullptr;
+  // Within one iteration the shade kernels of different material classes are independent of each other, and connect is
+  // independent of generate + extend: they are issued on separate streams so that small kernels overlap and the tail of
+  // one persistent kernel is filled by the blocks of the next (serial = one stream, used for per-stage timing).
+  const bool serial = timed || (r->flags & SPT_RENDER_SERIAL) != 0;
+  bool con_pending = false;
   auto iteration = [&]() {
+    if (con_pending) { cudaStreamWaitEvent(st, s->ev_con, 0); con_pending = false; } // logic resets the shadow-queue counters
     spt::launch_logic(ds, P, grid_logic, st); launches++;
     if (special) { spt::launch_special(ds, P, grid_shade, st); launches++; }
-    for (int m = 0; m < 8; m++) if (mats & (1u << m)) { spt::launch_shade(m, ds, P, count, grid_shade, st); launches++; }
-    if (!P.sort_materials) { spt::launch_shade(-1, ds, P, count, grid_shade, st); launches++; }
-    spt::launch_generate(ds, P, grid_gen, st); launches++;
-    if (timed) cudaEventRecord(s->sev[1], st);
-    spt::launch_connect(ds, P, count, grid_con, st);
-    if (timed) cudaEventRecord(s->sev[2], st);
-    spt::launch_extend(ds, P, count, grid_ext, st);
+    if (serial) {
+      for (int m = 0; m < 8; m++) if (mats & (1u << m)) { spt::launch_shade(m, ds, P, count, grid_shade, st); launches++; }
+      if (!P.sort_materials) { spt::launch_shade(-1, ds, P, count, grid_shade, st); launches++; }
+      spt::launch_generate(ds, P, grid_gen, st); launches++;
+      if (timed) cudaEventRecord(s->sev[1], st);
+      spt::launch_connect(ds, P, count, grid_con, st);
+      if (timed) cudaEventRecord(s->sev[2], st);
+      spt::launch_extend(ds, P, count, grid_ext, st);
+    } else {
+      cudaEventRecord(s->ev_fork, st);
+      int k = 0; bool used[2] = {false, false};
+      for (int m = 0; m < 8; m++) if (mats & (1u << m)) {
+        cudaStream_t sm = st;
+        if (k > 0) { const int j = (k - 1) & 1; sm = s->aux[j]; if (!used[j]) { cudaStreamWaitEvent(sm, s->ev_fork, 0); used[j] = true; } }
+        spt::launch_shade(m, ds, P, count, grid_shade, sm); launches++; k++;
+      }
+      if (!P.sort_materials) { spt::launch_shade(-1, ds, P, count, grid_shade, st); launches++; }
+      for (int j = 0; j < 2; j++) if (used[j]) { cudaEventRecord(s->ev_join[j], s->aux[j]); cudaStreamWaitEvent(st, s->ev_join[j], 0); }
+      cudaEventRecord(s->ev_shaded, st);
+      cudaStreamWaitEvent(s->aux[2], s->ev_shaded, 0);
+      spt::launch_connect(ds, P, count, grid_con, s->aux[2]);
+      cudaEventRecord(s->ev_con, s->aux[2]); con_pending = true;
+      spt::launch_generate(ds, P, grid_gen, st); launches++;
+      spt::launch_extend(ds, P, count, grid_ext, st);
+    }
     launches += 2; iters++;
   };
   if (r->max_depth > 0 && P.total_samples > 0) {
@@ -372,6 +407,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
         iteration();
         if (timed) cudaEventRecord(s->sev[3], st);
       }
+      if (con_pending) { cudaStreamWaitEvent(st, s->ev_con, 0); con_pending = false; }
       CU(cudaMemcpyAsync(s->h_ctr, s->ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, st));
       CU(cudaStreamSynchronize(st));
       CU(cudaGetLastError());

@@ -45,7 +45,6 @@ struct ConnectSrc { // the queued shadow rays: any hit (pt.rs:81, :169); unocclu
 template <bool COUNT>
 __global__ void __launch_bounds__(SPT_BLOCK) k_extend(const DScene sc, const RenderParams P) {
   TravCounters tc = {};
-  if (blockIdx.x == 0 && threadIdx.x == 0) { P.ctr->it.sq = 0; P.ctr->it.next_con = 0; } // connect of this iteration is done
   ExtendSrc src{P, 0};
   trace_persistent<false, COUNT>(sc, src, &P.ctr->it.next_ext, tc);
   warp_sum_to(&P.ctr->ext_rays, src.n_rays);

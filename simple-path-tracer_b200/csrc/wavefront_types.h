@@ -25,10 +25,10 @@ struct PathPool { // `n` slots
 struct ShadowQueue { float4* o; float4* d; float4* c; }; // o.xyz,tmin | d.xyz,tmax | contrib.rgb,pixel
 struct IterCounters { // per-iteration device counters; each is zeroed by a kernel that runs between its consumer and its next producer
   uint32_t q[SPT_NQ];   // shade-queue fill      (producer: logic/special, consumers: special/shade, zeroed by generate)
-  uint32_t sq;          // shadow-queue fill     (producer: special/shade, consumer: connect, zeroed by extend)
+  uint32_t sq;          // shadow-queue fill     (producer: special/shade, consumer: connect, zeroed by logic)
   uint32_t live;        // live slots after generate (read by the host; zeroed by logic)
   uint32_t next_ext;    // ray-fetch cursor of extend  (zeroed by logic)
-  uint32_t next_con;    // ray-fetch cursor of connect (zeroed by extend)
+  uint32_t next_con;    // ray-fetch cursor of connect (zeroed by logic)
   uint32_t pad[2];
 };
 struct DevCounters { // device-side totals of one render

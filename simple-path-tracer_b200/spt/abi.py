@@ -23,6 +23,7 @@ AGG = dict(group=0, bvh=1)
 RENDER_COUNT_TRAVERSAL = 1
 RENDER_NO_SORT = 2
 RENDER_TIME_STAGES = 4
+RENDER_SERIAL = 8
 
 
 class MeshDesc(C.Structure):

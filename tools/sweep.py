@@ -15,6 +15,7 @@ ap.add_argument("--pools", default="0")
 ap.add_argument("--lib", default="")
 ap.add_argument("--reps", type=int, default=3)
 ap.add_argument("--tag", default="")
+ap.add_argument("--serial", action="store_true", help="one stream (SPT_RENDER_SERIAL)")
 args = ap.parse_args()
 if args.lib:
     os.environ["SPT_LIB"] = args.lib
@@ -35,7 +36,8 @@ for item in args.items:
             st = sc.render_device(fb.data_ptr(), w, h, spp=spp, seed=rep + 1, pool_size=pool, flags=abi.RENDER_TIME_STAGES if rep else 0)
             if rep and (best is None or st["seconds_total"] < best["seconds_total"]):
                 best = st
-        plain = sc.render_device(fb.data_ptr(), w, h, spp=spp, seed=9, pool_size=pool)
+        plain = min((sc.render_device(fb.data_ptr(), w, h, spp=spp, seed=9 + i, pool_size=pool, flags=abi.RENDER_SERIAL if args.serial else 0) for i in range(3)),
+                    key=lambda st: st["seconds_total"])
         rays = best["ext_rays"] + best["shadow_rays"] + best["probe_rays"]
         print(json.dumps({"tag": args.tag, "scene": name, "spp": spp, "pool": pool, "mpaths_s": best["paths"] / best["seconds_total"] / 1e6,
                           "mpaths_s_untimed": plain["paths"] / plain["seconds_total"] / 1e6,
