@@ -1,0 +1,92 @@
+// main.cpp — command line of the reference binary (src/main.rs:26-68) on the CUDA core:
+//
+//   spt_host --scene S.json --renderer R.json [--width 512] [--height 512] --output out.png [--camera NAME]
+//
+// plus host-side options that have no counterpart in the reference:
+//   --renderer-type T   renderer arm to create (default pt_wavefront; the file's "pt" names the reference's CPU integrator)
+//   --base-path P       resolve relative obj_file / image_file / external JSON against P instead of the scene file
+//   --device N  --seed N  --pool N  --spp N (overrides the renderer file)
+//   --rank R --world-size W   render only the tiles rank R of W owns (one process per GPU)
+//   --raw FILE          also write the linear f32 mean image (height*width*3, row 0 = top)
+//   --dump-desc FILE    write the flattened scene (no GPU needed) and exit
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <memory>
+
+#include "host.h"
+
+using namespace spt_host;
+
+namespace {
+std::string ext_of(const std::string& path) { // loader/mod.rs:8-32 dispatches on the file extension
+  const size_t slash = path.find_last_of('/'), dot = path.find_last_of('.');
+  if (dot == std::string::npos || (slash != std::string::npos && dot < slash)) throw HostError("There is no file extension");
+  return path.substr(dot + 1);
+}
+} // namespace
+
+int main(int argc, char** argv) {
+  std::string scene_path, renderer_path, output, camera, base_path, dump, raw, renderer_type = "pt_wavefront";
+  bool has_camera = false;
+  int width = 512, height = 512, device = 0, pool = 0, spp = 0, rank = 0, world = 1;
+  uint64_t seed = 1;
+  for (int i = 1; i < argc; i++) {
+    const std::string a = argv[i];
+    auto val = [&]() -> std::string { if (i + 1 >= argc) { fprintf(stderr, "error: %s needs a value\n", a.c_str()); exit(2); } return argv[++i]; };
+    if (a == "--scene" || a == "-s") scene_path = val();
+    else if (a == "--renderer" || a == "-r") renderer_path = val();
+    else if (a == "--width" || a == "-w") width = atoi(val().c_str());
+    else if (a == "--height" || a == "-h") height = atoi(val().c_str());
+    else if (a == "--output" || a == "-o") output = val();
+    else if (a == "--camera" || a == "-c") { camera = val(); has_camera = true; }
+    else if (a == "--renderer-type") renderer_type = val();
+    else if (a == "--base-path") base_path = val();
+    else if (a == "--device") device = atoi(val().c_str());
+    else if (a == "--seed") seed = strtoull(val().c_str(), nullptr, 10);
+    else if (a == "--pool") pool = atoi(val().c_str());
+    else if (a == "--spp") spp = atoi(val().c_str());
+    else if (a == "--rank") rank = atoi(val().c_str());
+    else if (a == "--world-size") world = atoi(val().c_str());
+    else if (a == "--raw") raw = val();
+    else if (a == "--dump-desc") dump = val();
+    else { fprintf(stderr, "error: unknown argument '%s'\n", a.c_str()); return 2; }
+  }
+  try {
+    if (scene_path.empty()) throw HostError("--scene is required");
+    const std::string sext = ext_of(scene_path);
+    if (sext == "gltf") throw HostError("json - 'gltf' import is out of scope of the grafted path");
+    if (sext != "json") throw HostError("File extension '" + sext + "' is not recognized");
+    FlatScene fs = load_scene(scene_path, base_path);
+    for (const auto& w : fs.warnings) fprintf(stderr, "warning: %s\n", w.c_str());
+    if (!dump.empty()) { dump_scene(fs, dump); return 0; }
+    if (renderer_path.empty() || output.empty()) throw HostError("--renderer and --output are required");
+    const std::string rext = ext_of(renderer_path);
+    if (rext != "json") throw HostError("File extension '" + rext + "' is not recognized");
+    RendererConfig rc = load_renderer_config(renderer_path);
+    if (spp > 0) rc.sampler.spp = spp;
+    std::unique_ptr<Renderer> renderer(create_renderer(renderer_type.empty() ? rc.type : renderer_type, rc.max_depth, rc.sampler, rc.filter));
+    WavefrontPathTracer* wf = dynamic_cast<WavefrontPathTracer*>(renderer.get());
+    if (wf) { wf->seed = seed; wf->pool_size = pool; wf->rank = rank; wf->world_size = world; }
+    DeviceScene scene(fs, device);
+    OutputConfig oc; oc.width = width; oc.height = height; oc.output_filename = output; oc.used_camera_name = camera; oc.has_camera_name = has_camera;
+    const auto t0 = std::chrono::steady_clock::now();
+    const std::vector<float> mean = renderer->render(scene, oc);
+    const double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (!raw.empty()) { std::ofstream fh(raw, std::ios::binary); fh.write((const char*)mean.data(), (std::streamsize)(mean.size() * 4)); }
+    if (wf) {
+      const SptStats& st = wf->last_stats;
+      printf("{\"paths\": %llu, \"ext_rays\": %llu, \"shadow_rays\": %llu, \"probe_rays\": %llu, \"iterations\": %llu, \"kernel_launches\": %llu, "
+             "\"seconds_device\": %.6f, \"seconds_wall\": %.6f, \"mpaths_per_s\": %.3f}\n",
+             (unsigned long long)st.paths, (unsigned long long)st.ext_rays, (unsigned long long)st.shadow_rays, (unsigned long long)st.probe_rays,
+             (unsigned long long)st.iterations, (unsigned long long)st.kernel_launches, st.seconds_total, wall,
+             st.seconds_total > 0 ? st.paths / st.seconds_total / 1e6 : 0.0);
+    }
+  } catch (const std::exception& e) {
+    fprintf(stderr, "Error: %s\n", e.what());
+    return 1;
+  }
+  return 0;
+}

@@ -1,0 +1,262 @@
+"""The compiled C++ host (simple-path-tracer_b200/host/) against the Python mirror of the reference loader: both read the
+same scene JSON and must flatten it into the same SptSceneDesc (ints exact, floats to 1e-6: sin/cos of the instance
+rotations come from different libm's), reject the same malformed inputs, and — on the GPU — produce the same image."""
+import ctypes
+import json
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+from spt import abi, loader, scenes
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def host_bin(built):
+    import __graft_entry__ as g
+    return g.build_host()
+
+
+def read_dump(path):
+    out, buf, p = {}, open(path, "rb").read(), 0
+    while p < len(buf):
+        nl, = struct.unpack_from("<I", buf, p); p += 4
+        name = buf[p:p + nl].decode(); p += nl
+        nb, = struct.unpack_from("<Q", buf, p); p += 8
+        out[name] = buf[p:p + nb]; p += nb
+    return out
+
+
+def struct_bytes(arr, n, size=None):
+    size = size or ctypes.sizeof(arr._type_)
+    return b"".join(ctypes.string_at(ctypes.addressof(arr[i]), size) for i in range(n))
+
+
+def python_dump(fs):
+    d = fs.to_desc()
+    out = {}
+    for i, m in enumerate(fs.meshes):
+        for k in ("positions", "normals", "texcoords", "tangents", "bitangents"):
+            out[f"mesh{i}.{k}"] = np.ascontiguousarray(m[k], np.float32).tobytes()
+        out[f"mesh{i}.indices"] = np.ascontiguousarray(m["indices"], np.uint32).tobytes()
+    out["spheres"] = struct_bytes(d.spheres, d.n_spheres)
+    out["instances"] = struct_bytes(d.instances, d.n_instances)
+    out["surfaces"] = struct_bytes(d.surfaces, d.n_surfaces)
+    out["materials"] = struct_bytes(d.materials, d.n_materials)
+    out["textures"] = struct_bytes(d.textures, d.n_textures, abi.TextureDesc.rgba.offset)
+    for i, t in enumerate(fs.textures):
+        if t["rgba"] is not None:
+            out[f"texture{i}.rgba"] = np.ascontiguousarray(t["rgba"], np.uint8).tobytes()
+    out["mediums"] = struct_bytes(d.mediums, d.n_mediums)
+    out["lights"] = struct_bytes(d.lights, d.n_lights)
+    out["cameras"] = struct_bytes(d.cameras, d.n_cameras)
+    if fs.env is not None:
+        out["env.size"] = struct.pack("<ii", fs.env["width"], fs.env["height"])
+        out["env.scale"] = np.asarray(fs.env["scale"], np.float32).tobytes()
+        out["env.rgb"] = np.ascontiguousarray(fs.env["rgb"], np.float32).tobytes()
+    out["misc"] = struct.pack("<iii", fs.env_light_index, fs.light_sampler, fs.aggregate)
+    out["warnings"] = "".join(w + "\n" for w in fs.warnings).encode()
+    return out
+
+
+def words_match(a, b, tol=2e-6):
+    """every 4-byte word equal as an integer, or close as a float"""
+    assert len(a) == len(b)
+    ia, ib = np.frombuffer(a, np.int32), np.frombuffer(b, np.int32)
+    fa, fb = np.frombuffer(a, np.float32), np.frombuffer(b, np.float32)
+    with np.errstate(invalid="ignore", over="ignore"):
+        close = np.abs(fa - fb) <= tol * np.maximum(1.0, np.abs(fa))
+    return (ia == ib) | close
+
+
+def run_host(host_bin, args, check=True):
+    r = subprocess.run([host_bin] + args, capture_output=True, text=True)
+    if check:
+        assert r.returncode == 0, r.stderr
+    return r
+
+
+def dump_via_host(host_bin, tmp_path, scene_dict, name="scene"):
+    sj = tmp_path / f"{name}.json"
+    sj.write_text(json.dumps(scene_dict))
+    out = tmp_path / f"{name}.dump"
+    run_host(host_bin, ["--scene", str(sj), "--base-path", scenes.BASE_PATH, "--dump-desc", str(out)])
+    return read_dump(out)
+
+
+@pytest.mark.parametrize("name", ["c1", "c1b", "c2", "c3", "c4", "c5"])
+def test_cpp_loader_flattens_like_the_python_loader(host_bin, tmp_path, name):
+    sd = scenes.CONFIGS[name]["scene"]()
+    got = dump_via_host(host_bin, tmp_path, sd)
+    want = python_dump(loader.load_scene(sd, scenes.BASE_PATH))
+    assert sorted(got) == sorted(want)
+    for k in want:
+        if k.endswith(".indices") or k.endswith(".rgba") or k in ("warnings", "misc", "env.size"):
+            assert got[k] == want[k], k
+        elif k == "env.rgb":  # float64 sin/cos/acos from two libm's: a texel on the sun disc's edge may flip
+            ok = words_match(got[k], want[k], 1e-5)
+            assert ok.mean() > 0.9999, k
+        else:
+            ok = words_match(got[k], want[k])
+            assert ok.all(), (k, int((~ok).sum()))
+
+
+TEXTURED = {
+    "cameras": {"type": "perspective", "name": "cam_a", "eye": [0.0, 0.0, 5.0], "forward": [0.0, 0.0, -1.0], "up": [0.0, 1.0, 0.0], "fov": 45.0},
+    "textures": [
+        {"type": "scalar", "name": "a", "value": [0.5, 0.25, 1.0]},
+        {"type": "scalar", "name": "b", "value": [0.2, 0.2, 0.2], "is_srgb": True},
+        {"type": "image_array", "name": "img", "rgba": [[[255, 0, 0, 255], [0, 255, 0, 255]], [[0, 0, 255, 255], [255, 255, 255, 128]]],
+         "tiling": [2.0, 3.0], "wrap": "mirror_repeat", "#comment": "ignored"},
+        {"type": "mul", "name": "ab", "t1": "a", "t2": "b"},
+        {"type": "div", "name": "pos", "t1": "ab", "t2": "a", "mode": "position", "offset": [0.5, 0.5, 0.25], "bogus": 1.0},
+    ],
+    "materials": [{"type": "lambert", "name": "m0", "albedo": "ab"},
+                  {"type": "plastic", "name": "m1", "int_ior": 1.5, "ext_ior": 1.1, "albedo": "img", "roughness_x": "a", "roughness_y": "b"},
+                  {"type": "pbr_specular", "name": "m2", "diffuse": "pos", "specular": "a", "roughness": "b"}],
+    "mediums": [{"type": "homogeneous", "name": "fog", "sigma_a": [0.1, 0.2, 0.3], "sigma_s": [9.0, 9.0, 9.0], "asymmetric": 0.3}],
+    "primitives": [{"type": "sphere", "name": "s", "radius": 0.5, "center": [0.0, 1.0, 0.0]},
+                   {"type": "trimesh", "name": "cube", "obj_file": "cube.npz"},
+                   {"type": "cubic_bezier", "name": "skipped", "whatever": 1}],
+    "surfaces": [{"name": "sf", "material": "m1", "normal_map": "img", "emissive": [1.0, 2.0, 3.0], "emissive_map": "a",
+                  "double_sided": True, "inside_medium": "fog"}],
+    "instances": [{"name": "zz", "primitive": "s", "material": "m0", "translate": [1.0, 2.0, 3.0]},
+                  {"name": "aa", "primitive": "cube", "surface": "sf", "scale": [1.0, 2.0, 0.5], "rotate": [10.0, 20.0, 30.0],
+                   "matrix": [1.0, 0.0, 0.0, 0.0, 0.0, 1.0, 0.5, 0.0, 0.0, 0.0, 1.0, 0.0, 0.25, 0.5, 0.75, 1.0]},
+                  {"name": "mm", "primitive": "cube", "material": "m2"}],
+    "lights": [{"type": "spot", "name": "sp", "position": [0.0, 4.0, 0.0], "direction": [0.0, -1.0, 0.0], "inner_angle": 20.0,
+                "strength": [10.0, 10.0, 10.0]},
+               {"type": "point", "name": "pt", "position": [1.0, 1.0, 1.0], "strength": [1.0, 1.0, 1.0]},
+               {"type": "directional", "name": "dl", "direction": [0.0, -1.0, 0.5], "strength": [2.0, 2.0, 2.0]}],
+    "environment": {"type": "color", "color": [0.1, 0.2, 0.3], "scale": [2.0, 2.0, 2.0]},
+    "light_sampler": "power_is",
+}
+
+
+def test_cpp_loader_covers_every_component_kind(host_bin, tmp_path):
+    """textures with srgb / input-modifier wrappers, every light kind, medium (Q13), explicit surface, matrix+SRT
+    instance transforms, name-sorted instances and lights (Q9), env light index (Q8), unused-key warnings."""
+    got = dump_via_host(host_bin, tmp_path, TEXTURED)
+    fs = loader.load_scene(TEXTURED, scenes.BASE_PATH)
+    want = python_dump(fs)
+    assert sorted(got) == sorted(want)
+    for k in want:
+        if k.endswith(".indices") or k.endswith(".rgba") or k in ("warnings", "misc", "env.size"):
+            assert got[k] == want[k], k
+        else:
+            assert words_match(got[k], want[k]).all(), k
+    assert b"bogus" in got["warnings"] and b"skipped" in got["warnings"]
+    assert fs.env_light_index == 3 and len(fs.lights) == 5  # 3 explicit + env + 1 shape light
+
+
+def _broken(**patch):
+    sd = json.loads(json.dumps(scenes.c1b()))
+    sd.update(patch)
+    return sd
+
+
+@pytest.mark.parametrize("mutate, message", [
+    (lambda s: s["cameras"].update(fov=45), "'fov' should be float"),  # Q23
+    (lambda s: s["materials"][0].update(albedo="nope"), "There is no texture named 'nope'"),
+    (lambda s: s["textures"].append(dict(s["textures"][0])), "Duplicated texture name"),
+    (lambda s: s.pop("lights"), "There is no 'lights' field"),
+    (lambda s: s["instances"][0].update(primitive="ghost"), "There is no primitive named 'ghost'"),
+    (lambda s: s["primitives"].append({"type": "torus", "name": "t"}), "unknown type 'torus'"),
+    (lambda s: s.update(aggregate="octree"), "Unknown aggregate type 'octree'"),
+    (lambda s: s.update(gltf="x.gltf"), "out of scope"),
+    (lambda s: s.update(environment=[{"type": "color", "color": [1.0, 1.0, 1.0]}]), "Field should not be an array"),
+])
+def test_cpp_loader_rejects_what_the_python_loader_rejects(host_bin, tmp_path, mutate, message):
+    sd = json.loads(json.dumps(scenes.c1b()))
+    mutate(sd)
+    with pytest.raises(loader.SceneError, match=message.replace("(", r"\(")):
+        loader.load_scene(sd, scenes.BASE_PATH)
+    sj = tmp_path / "bad.json"
+    sj.write_text(json.dumps(sd))
+    r = run_host(host_bin, ["--scene", str(sj), "--base-path", scenes.BASE_PATH, "--dump-desc", str(tmp_path / "x.dump")], check=False)
+    assert r.returncode == 1 and message in r.stderr, r.stderr
+
+
+def test_cpp_host_external_files_obj_and_png(host_bin, tmp_path):
+    """external JSON sections (json.rs:212-242), an .obj mesh with shared corners + a quad (tobj triangulation, Q22 with two
+    objects), and a PNG image texture written by PIL and decoded by the host's own reader."""
+    from PIL import Image
+    rng = np.random.RandomState(5)
+    img = rng.randint(0, 256, (5, 7, 3), dtype=np.uint8)
+    Image.fromarray(img).save(tmp_path / "tex.png")
+    (tmp_path / "quad.obj").write_text(
+        "v -1 0 -1\nv 1 0 -1\nv 1 0 1\nv -1 0 1\nvt 0 0\nvt 1 0\nvt 1 1\nvt 0 1\nvn 0 1 0\n"
+        "o first\nf 1/1/1 2/2/1 3/3/1\n"  # 3 vertices, 3 indices: Q22's offset (index count) happens to equal the vertex count
+        "o second\nv 0 1 0\nf 1/1/1 2/2/1 3/3/1 4/4/1\nf -1/3/1 2/2/1 3/3/1\n")
+    (tmp_path / "mats.json").write_text(json.dumps([{"type": "lambert", "name": "m", "albedo": "t"}]))
+    sd = {"cameras": {"type": "perspective", "name": "c", "eye": [0.0, 1.0, 4.0], "forward": [0.0, 0.0, -1.0], "up": [0.0, 1.0, 0.0], "fov": 50.0},
+          "textures": [{"type": "image", "name": "t", "image_file": "tex.png", "is_srgb": True}],
+          "materials": "mats.json", "mediums": [],
+          "primitives": [{"type": "trimesh", "name": "q", "obj_file": "quad.obj"}],
+          "surfaces": [], "instances": [{"name": "i", "primitive": "q", "material": "m"}],
+          "lights": [{"type": "point", "name": "p", "position": [0.0, 3.0, 0.0], "strength": [9.0, 9.0, 9.0]}]}
+    sj = tmp_path / "scene.json"
+    sj.write_text(json.dumps(sd))
+    out = tmp_path / "scene.dump"
+    run_host(host_bin, ["--scene", str(sj), "--dump-desc", str(out)])
+    got = read_dump(out)
+    want = python_dump(loader.load_scene(str(sj)))
+    assert sorted(got) == sorted(want)
+    for k in want:
+        if k.endswith(".indices") or k.endswith(".rgba") or k in ("warnings", "misc"):
+            assert got[k] == want[k], k
+        else:
+            assert words_match(got[k], want[k]).all(), k
+    assert len(got["mesh0.indices"]) == 4 * 3 * 4  # triangle + quad (2 triangles) + triangle
+    (tmp_path / "quad.obj").write_text("v 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\no a\nf 1 2 3 4\no b\nf 1 2 3\n")  # Q22 overruns
+    with pytest.raises(Exception):
+        loader.load_scene(str(sj))
+    r = run_host(host_bin, ["--scene", str(sj), "--dump-desc", str(out)], check=False)
+    assert r.returncode == 1 and "out of range" in r.stderr
+
+
+def test_cpp_renderer_config_and_cli_errors(host_bin, tmp_path):
+    sj = tmp_path / "s.json"
+    sj.write_text(json.dumps(scenes.c1()))
+    rj = tmp_path / "r.json"
+    rj.write_text(json.dumps({"type": "pt", "max_depth": 8.0, "sampler": {"type": "recurrence", "spp": 4}, "filter": {"type": "box", "radius": 0.5}}))
+    r = run_host(host_bin, ["--scene", str(sj), "--renderer", str(rj), "--output", str(tmp_path / "o.png")], check=False)
+    assert r.returncode == 1 and "'max_depth' shoule be integer" in r.stderr
+    rj.write_text(json.dumps(scenes.PT_JSON))
+    r = run_host(host_bin, ["--scene", str(sj), "--renderer", str(rj), "--renderer-type", "pt", "--output", str(tmp_path / "o.png")], check=False)
+    assert r.returncode == 1 and "CPU integrator" in r.stderr
+    r = run_host(host_bin, ["--scene", str(tmp_path / "s.txt"), "--dump-desc", "x"], check=False)
+    assert r.returncode == 1 and "File extension 'txt' is not recognized" in r.stderr
+    if not os.path.exists("/dev/nvidiactl"):  # no GPU here: the product must fail loudly, not fall back
+        r = run_host(host_bin, ["--scene", str(sj), "--renderer", str(rj), "--output", str(tmp_path / "o.png")], check=False)
+        assert r.returncode == 1 and "spt_context_create" in r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["c1b", "c4"])
+def test_cpp_host_render_equals_python_host_render(host_bin, tmp_path, ctx, name):
+    """same scene, same seed: the C++ host (spt_host CLI) and the Python host drive the same kernels -> same image."""
+    from PIL import Image
+    from spt import core
+    sd = scenes.CONFIGS[name]["scene"]()
+    sj, rj = tmp_path / "s.json", tmp_path / "pt.json"
+    sj.write_text(json.dumps(sd))
+    rj.write_text(json.dumps(dict(scenes.PT_JSON, sampler={"type": "recurrence", "spp": 8})))
+    png, raw = tmp_path / "o.png", tmp_path / "o.f32"
+    r = run_host(host_bin, ["--scene", str(sj), "--base-path", scenes.BASE_PATH, "--renderer", str(rj), "--width", "160", "--height", "96",
+                            "--output", str(png), "--raw", str(raw), "--seed", "7"])
+    stats = json.loads(r.stdout.strip().splitlines()[-1])
+    assert stats["paths"] == 160 * 96 * 8 and stats["kernel_launches"] > 0
+    got = np.fromfile(raw, np.float32).reshape(96, 160, 3)
+    sc = core.Scene(ctx, loader.load_scene(sd, scenes.BASE_PATH))
+    want, rgb8, _ = sc.render(160, 96, spp=8, seed=7, want_rgb8=True)
+    sc.close()
+    rel = np.abs(got - want) / (np.abs(want) + 1e-3)
+    assert (rel.max(-1) < 1e-3).mean() > 0.995  # rotations differ in the last ulp between the two hosts' libm
+    disk = np.asarray(Image.open(png).convert("RGB"))
+    assert disk.shape == (96, 160, 3)
+    assert (np.abs(disk.astype(int) - rgb8.astype(int)) <= 1).mean() > 0.995
