@@ -85,3 +85,19 @@ def test_fails_loudly_without_gpu(built):
     with pytest.raises(abi.SptError) as e:
         core.Context(0)
     assert "no CUDA device" in str(e.value) or "CUDA" in str(e.value)
+
+
+def test_rust_ffi_is_in_sync():
+    """rust_shim/src/renderer/ffi.rs is generated from include/spt.h; it must match the header as committed, and
+    declare every struct and entry point the Python mirror binds."""
+    import importlib.util
+    from spt import abi
+    spec = importlib.util.spec_from_file_location("gen_rust_ffi", os.path.join(ROOT, "tools", "gen_rust_ffi.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    text = open(gen.OUT).read()
+    assert text == gen.generate()
+    for sym in abi.SYMBOLS:
+        assert f"pub fn {sym}(" in text, sym
+    for st in ("SptSceneDesc", "SptRenderDesc", "SptStats", "SptRay", "SptHit", "SptTextureDesc", "SptBxdfQuery", "SptBxdfResult"):
+        assert f"pub struct {st} {{" in text, st
