@@ -155,10 +155,16 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    reduce_events = []
+
     def step(seed, flags=0):
         st = sc.render_device(fb.data_ptr(), w, h, seed=seed, flags=flags, **kw)
         if world > 1:
+            r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            r0.record()
             dist.reduce(fb, dst=0, op=dist.ReduceOp.SUM)  # framebuffer gather over NVLink (disjoint tiles: exact)
+            r1.record()
+            reduce_events.append((r0, r1))
         return st
 
     for i in range(W):
@@ -168,10 +174,26 @@ def main():
     if sampler:
         sampler.start()
     barrier()
+    reduce_events.clear()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
+    ev0.record()  # spt_render_device returns after its own stream has drained, so events on this stream bracket the device work
     stats = [step(i + 1) for i in range(args.steps)]
+    ev1.record()
     barrier()
-    elapsed = time.perf_counter() - t0
+    wall = time.perf_counter() - t0
+    elapsed = ev0.elapsed_time(ev1) * 1e-3
+    # per-rank breakdown of the timed region: device time inside spt_render_device (CUDA events on the library's stream)
+    # and of the NCCL framebuffer reduce
+    render_ms = 1e3 * sum(s_["seconds_total"] for s_ in stats) / args.steps
+    reduce_ms = sum(a.elapsed_time(b) for a, b in reduce_events) / args.steps if reduce_events else 0.0
+    brk = torch.tensor([render_ms, reduce_ms, 1e3 * wall / args.steps], dtype=torch.float64, device=dev)
+    brk_all = [torch.zeros_like(brk) for _ in range(world)]
+    if world > 1:
+        dist.all_gather(brk_all, brk)
+    else:
+        brk_all = [brk]
+    brk_list = [b.tolist() for b in brk_all]
     tt = torch.tensor([elapsed], dtype=torch.float64, device=dev)
     agg = torch.tensor([sum(s[k] for s in stats) for k in ("paths", "ext_rays", "shadow_rays", "probe_rays", "kernel_launches")],
                        dtype=torch.float64, device=dev)
@@ -249,6 +271,9 @@ def main():
         "shadow_rays_culled_per_path": sum(s["shadow_culled"] for s in stats) / max(1.0, sum(s["paths"] for s in stats)),
         "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(w * h * 3 * 4)},
         "gpu_launches": int(launches), "roofline": roofline, "clocks": sampler.summary() if sampler else None,
+        "timing": {"source": "CUDA events bracketing the K steps, max over ranks", "wall_ms_per_step": float(max(b[2] for b in brk_list)),
+                   "render_device_ms_per_rank": [round(float(b[0]), 3) for b in brk_list],
+                   "reduce_ms_per_rank": [round(float(b[1]), 3) for b in brk_list]},
     }
     if world == 1 and not args.no_cpu_baseline:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))

@@ -37,7 +37,7 @@ struct SptScene {
   void* pool_mem = nullptr; size_t pool_bytes = 0; int pool_n = 0;
   long long* film = nullptr; size_t film_px = 0;
   DevCounters* ctr = nullptr; uint32_t* batch_next = nullptr;
-  uint32_t* tiles = nullptr; size_t tiles_cap = 0;
+  uint32_t* tiles = nullptr; size_t tiles_cap = 0, n_tiles = 0; int tile_key[6] = {0, 0, 0, 0, 0, 0};
   float* out_mean = nullptr; uint8_t* out_rgb8 = nullptr; size_t out_px = 0;
   DevCounters* h_ctr = nullptr; // pinned
   cudaStream_t stream = nullptr;
@@ -287,7 +287,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   const int world = std::max(1, r->world_size), rank = r->rank;
   if (rank < 0 || rank >= world) return fail(SPT_ERR_INVALID, "spt_render: bad rank");
   const int spp = r->sampler_kind == SPT_SAMPLER_JITTERED ? std::max(1, r->div_x) * std::max(1, r->div_y) : std::max(1, r->spp);
-  const int tw = r->tile_w > 0 ? r->tile_w : 32, th = r->tile_h > 0 ? r->tile_h : 32;
+  const int tw = r->tile_w > 0 ? r->tile_w : SPT_DEFAULT_TILE_W, th = r->tile_h > 0 ? r->tile_h : SPT_DEFAULT_TILE_H;
   if (tw % 8 || th % 4) return fail(SPT_ERR_INVALID, "spt_render: tile_w must be a multiple of 8 and tile_h of 4");
   CU(cudaSetDevice(s->ctx->device));
   cudaStream_t st = s->stream;
@@ -320,15 +320,20 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   P.ctr = s->ctr; P.film = s->film;
   // ---- tile ownership: tiles sorted by a hash, dealt round-robin -> interleaved, balanced to +-1 tile
   const int tiles_x = (r->width + tw - 1) / tw;
-  const std::vector<uint32_t> mine = owned_tiles(r->width, r->height, tw, th, rank, world);
-  if (s->tiles_cap < mine.size()) { cudaFree(s->tiles); s->tiles = nullptr; CU(cudaMalloc(&s->tiles, std::max<size_t>(1, mine.size()) * sizeof(uint32_t))); s->tiles_cap = mine.size(); }
-  if (!mine.empty()) CU(cudaMemcpyAsync(s->tiles, mine.data(), mine.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
-  P.tiles = s->tiles; P.n_tiles = (int)mine.size(); P.tiles_x = tiles_x; P.tile_w = tw; P.tile_h = th;
+  const int tile_key[6] = {r->width, r->height, tw, th, rank, world};
+  if (!s->tiles || memcmp(tile_key, s->tile_key, sizeof(tile_key)) != 0) { // the list only depends on these six numbers: keep it across renders
+    const std::vector<uint32_t> mine = owned_tiles(r->width, r->height, tw, th, rank, world);
+    if (s->tiles_cap < mine.size() || !s->tiles) { cudaFree(s->tiles); s->tiles = nullptr; CU(cudaMalloc(&s->tiles, std::max<size_t>(1, mine.size()) * sizeof(uint32_t))); s->tiles_cap = std::max<size_t>(1, mine.size()); }
+    if (!mine.empty()) CU(cudaMemcpy(s->tiles, mine.data(), mine.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    s->n_tiles = mine.size();
+    memcpy(s->tile_key, tile_key, sizeof(tile_key));
+  }
+  P.tiles = s->tiles; P.n_tiles = (int)s->n_tiles; P.tiles_x = tiles_x; P.tile_w = tw; P.tile_h = th;
   P.width = r->width; P.height = r->height; P.max_depth = r->max_depth;
   P.sampler = r->sampler_kind; P.spp = spp; P.div_x = std::max(1, r->div_x); P.div_y = std::max(1, r->div_y);
   P.seed = r->seed;
   P.sort_materials = (r->flags & SPT_RENDER_NO_SORT) ? 0 : 1;
-  P.total_samples = (unsigned long long)mine.size() * (unsigned long long)(tw * th) * (unsigned long long)spp;
+  P.total_samples = (unsigned long long)s->n_tiles * (unsigned long long)(tw * th) * (unsigned long long)spp;
   DScene ds = s->ds;
   ds.camera = s->cameras[r->camera_index];
   const bool count = (r->flags & SPT_RENDER_COUNT_TRAVERSAL) != 0;
@@ -393,6 +398,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
     // `stride` iterations (the cursor tells how far the render is); once the cursor is exhausted the pool drains
     // within max_depth iterations and the host looks after every one.
     const uint64_t est_total = std::max<uint64_t>(1, P.total_samples / (uint64_t)pool_n);
+    bool drain_seen = false;
     for (;;) {
       int stride = 1;
       if (!timed && iters > 0 && s->h_ctr->cursor < P.total_samples) {
@@ -400,6 +406,12 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
         const double per_iter = done / (double)iters;                       // fraction of the samples started per iteration
         const double left = per_iter > 0 ? (1.0 - done) / per_iter : 1.0;   // iterations until the cursor runs out
         stride = (int)std::max(1.0, std::min(64.0, left * 0.5));
+      } else if (!timed && iters > 0 && !drain_seen) {
+        // first look after the last camera sample started: a path lives at most max_depth iterations, so issue most of
+        // the drain back to back (iterations over an empty pool cost a few tens of microseconds) instead of idling the
+        // GPU on a host round trip after each one
+        drain_seen = true;
+        stride = std::max(1, r->max_depth - 2);
       }
       (void)est_total;
       for (int k = 0; k < stride; k++) {
@@ -464,7 +476,7 @@ extern "C" int32_t spt_render(SptScene* s, const SptRenderDesc* r, float* out_rg
 
 extern "C" int32_t spt_owned_tiles(int32_t width, int32_t height, int32_t tile_w, int32_t tile_h, int32_t rank, int32_t world_size,
                                    uint32_t* out, int64_t cap, int64_t* n_out) {
-  const int tw = tile_w > 0 ? tile_w : 32, th = tile_h > 0 ? tile_h : 32;
+  const int tw = tile_w > 0 ? tile_w : SPT_DEFAULT_TILE_W, th = tile_h > 0 ? tile_h : SPT_DEFAULT_TILE_H;
   if (width <= 0 || height <= 0 || world_size <= 0 || rank < 0 || rank >= world_size || !n_out) return fail(SPT_ERR_INVALID, "spt_owned_tiles: bad argument");
   const std::vector<uint32_t> mine = owned_tiles(width, height, tw, th, rank, world_size);
   *n_out = (int64_t)mine.size();

@@ -42,8 +42,16 @@ struct ConnectSrc { // the queued shadow rays: any hit (pt.rs:81, :169); unocclu
   }
 };
 
+// Tuning builds may force a register budget with -DSPT_TRAV_MINB=n (resident blocks per SM).  Measured on C2/C3/C5: the
+// unconstrained allocation (72 registers, 7 blocks/SM) beats both n=8 (64 registers, -2 %) and n=1 (-18 %).
+#ifdef SPT_TRAV_MINB
+#define SPT_TRAV_BOUNDS __launch_bounds__(SPT_BLOCK, SPT_TRAV_MINB)
+#else
+#define SPT_TRAV_BOUNDS __launch_bounds__(SPT_BLOCK)
+#endif
+
 template <bool COUNT>
-__global__ void __launch_bounds__(SPT_BLOCK) k_extend(const DScene sc, const RenderParams P) {
+__global__ void SPT_TRAV_BOUNDS k_extend(const DScene sc, const RenderParams P) {
   TravCounters tc = {};
   ExtendSrc src{P, 0};
   trace_persistent<false, COUNT>(sc, src, &P.ctr->it.next_ext, tc);
@@ -52,7 +60,7 @@ __global__ void __launch_bounds__(SPT_BLOCK) k_extend(const DScene sc, const Ren
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(SPT_BLOCK) k_connect(const DScene sc, const RenderParams P) {
+__global__ void SPT_TRAV_BOUNDS k_connect(const DScene sc, const RenderParams P) {
   TravCounters tc = {};
   ConnectSrc src{P, P.ctr->it.sq, 0};
   trace_persistent<true, COUNT>(sc, src, &P.ctr->it.next_con, tc);
@@ -91,7 +99,7 @@ struct BatchSrc {
 };
 
 template <bool ANY, bool COUNT>
-__global__ void __launch_bounds__(SPT_BLOCK) k_batch(const DScene sc, const float4* __restrict__ rays, uint32_t n, HitIO* __restrict__ hits,
+__global__ void SPT_TRAV_BOUNDS k_batch(const DScene sc, const float4* __restrict__ rays, uint32_t n, HitIO* __restrict__ hits,
                                                      uint8_t* __restrict__ occ, uint32_t* next, DevCounters* ctr) {
   TravCounters tc = {};
   BatchSrc src{sc, rays, n, hits, occ};

@@ -57,6 +57,19 @@ SPT_D void ray_setup(RaySetup& r, float3 o, float3 d) {
   r.octinv4 = (7u - oct) * 0x01010101u;
 }
 
+// float(byte j of x).  I2F.U8 runs on the XU pipe (4 lanes/clk per scheduler: ncu showed XU at 50 % of its peak with 48
+// conversions per node step); SPT_BYTE2F_MAGIC=1 builds 2^23 + q with one PRMT and subtracts 2^23 (ALU + FMA pipes, exact).
+#ifndef SPT_BYTE2F_MAGIC
+#define SPT_BYTE2F_MAGIC 0
+#endif
+SPT_D float byte_to_float(uint32_t x, int j) { // j is a compile-time constant after unrolling
+#if SPT_BYTE2F_MAGIC
+  return __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7650u | (uint32_t)j)) - 8388608.0f;
+#else
+  return (float)((x >> (8 * j)) & 0xff);
+#endif
+}
+
 // Slab test of the 8 quantised child boxes of one node; returns the node-group / primitive-group pair.
 SPT_D void node_children(const float4* __restrict__ nodes, uint32_t node_index, const RaySetup& r, float tmin, float tmax,
                          uint2& ng, uint2& tg) {
@@ -88,9 +101,9 @@ SPT_D void node_children(const float4* __restrict__ nodes, uint32_t node_index, 
 #pragma unroll
     for (int j = 0; j < 4; j++) {
       const int sh = 8 * j;
-      const float t0x = fmaf((float)((nearx >> sh) & 0xff), ax, bx), t1x = fmaf((float)((farx >> sh) & 0xff), ax, bx);
-      const float t0y = fmaf((float)((neary >> sh) & 0xff), ay, by), t1y = fmaf((float)((fary >> sh) & 0xff), ay, by);
-      const float t0z = fmaf((float)((nearz >> sh) & 0xff), az, bz), t1z = fmaf((float)((farz >> sh) & 0xff), az, bz);
+      const float t0x = fmaf(byte_to_float(nearx, j), ax, bx), t1x = fmaf(byte_to_float(farx, j), ax, bx);
+      const float t0y = fmaf(byte_to_float(neary, j), ay, by), t1y = fmaf(byte_to_float(fary, j), ay, by);
+      const float t0z = fmaf(byte_to_float(nearz, j), az, bz), t1z = fmaf(byte_to_float(farz, j), az, bz);
       const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
       const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax)) * 1.000002f; // conservative against rounding (incl. the approximate 1/d)
       if (cmin <= cmax) hitmask |= ((cb4 >> sh) & 0xffu) << ((bit4 >> sh) & 0xffu);

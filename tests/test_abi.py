@@ -56,11 +56,12 @@ def test_host_only_entry_points(built):
     assert lib.spt_version() >= 100
     import numpy as np
     for (w, h, world) in [(1920, 1080, 1), (1920, 1080, 2), (3840, 2160, 8), (70, 50, 4), (31, 5, 3)]:
-        tiles = [core.owned_tiles(w, h, r, world) for r in range(world)]
-        allt = np.concatenate(tiles)
-        n_all = ((w + 31) // 32) * ((h + 31) // 32)
-        assert len(allt) == n_all and len(set(allt.tolist())) == n_all          # complete and disjoint
-        assert max(len(t) for t in tiles) - min(len(t) for t in tiles) <= 1       # balanced
+        for tile, (tw, th) in (((0, 0), (8, 4)), ((32, 32), (32, 32))):  # 0 = SPT_DEFAULT_TILE_W x SPT_DEFAULT_TILE_H
+            tiles = [core.owned_tiles(w, h, r, world, tile) for r in range(world)]
+            allt = np.concatenate(tiles)
+            n_all = ((w + tw - 1) // tw) * ((h + th - 1) // th)
+            assert len(allt) == n_all and len(set(allt.tolist())) == n_all          # complete and disjoint
+            assert max(len(t) for t in tiles) - min(len(t) for t in tiles) <= 1       # balanced
     # interleaving: with 8 ranks, no rank owns a run of 8 consecutive tiles
     t0 = core.owned_tiles(3840, 2160, 0, 8)
     assert np.max(np.convolve((np.diff(t0) == 1).astype(int), np.ones(7, int))) < 7
