@@ -250,6 +250,22 @@ def main():
             traffic = json.load(fh).get("dram_bytes_per_launch")
     except OSError:
         pass
+    # regime (i) of SURVEY §8d: the scene is L2-resident, so the node / triangle / instance fetches are bounded by the
+    # L2 -> SM read bandwidth, measured here with a 16-byte-load microbenchmark over a 32 MB read-only set
+    l2 = None
+    try:
+        import ctypes
+        bl = ctypes.CDLL(os.path.join(ROOT, "simple-path-tracer_b200", "lib", "libspt_benchkernels.so"))
+        bl.spt_bench_l2_read_gbs.argtypes = [ctypes.c_int, ctypes.c_size_t, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
+        g = ctypes.c_double()
+        if bl.spt_bench_l2_read_gbs(local, 32 << 20, 64, 5, ctypes.byref(g)) == 0:
+            scene_bytes_per_ray = 80.0 * n_node + 48.0 * n_tri + 64.0 * n_inst
+            l2_achieved = rays_per_launch * scene_bytes_per_ray / max(ext_seconds / max(1, ext_launches), 1e-12) / 1e9
+            l2 = {"peak_gbs": g.value, "peak_source": "ld.global.cg.v4 over a 32 MB set, best of 5 (simple-path-tracer_b200/bench_kernels/l2_peak.cu)",
+                  "achieved_gbs": l2_achieved, "frac": l2_achieved / g.value,
+                  "what": "algorithmic node + triangle + instance bytes per ray x rays/s of k_extend (requests that hit L1 never reach L2)"}
+    except OSError:
+        pass
     pool_slots = args.pool or min(1 << 22, max(1 << 16, w * h * spp))
     roofline = {"bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                 "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
@@ -258,6 +274,7 @@ def main():
                 "grays_per_s": rays_per_launch / max(ext_seconds / max(1, ext_launches), 1e-12) / 1e9,
                 "stage_seconds": {"extend": s0["seconds_stage"][1], "shade": s0["seconds_stage"][2], "connect": s0["seconds_stage"][3],
                                   "total": s0["seconds_total"]},
+                "l2": l2,
                 "note": "scene working set (%.2f MB) is L2-resident: the HBM figure is the contract's denominator, the binding roof is instruction issue (ncu: issue-active 73 %%, 13/32 active lanes)" % (info["bytes_total"] / 1e6)}
     out = {
         "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": W,
