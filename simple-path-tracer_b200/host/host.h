@@ -96,6 +96,21 @@ class DeviceScene {
   SptScene* scene_ = nullptr;
 };
 
+// One process per GPU: rank `rank` of `world_size`, joined over NCCL (multi_gpu.cpp).
+class RankGroup {
+ public:
+  RankGroup(int rank, int world_size, int device, const std::string& id_file);
+  ~RankGroup();
+  RankGroup(const RankGroup&) = delete;
+  RankGroup& operator=(const RankGroup&) = delete;
+  std::vector<float> render_and_gather(DeviceScene& scene, const SptRenderDesc& rd, SptStats* stats, double* reduce_ms);
+  const int rank, world_size;
+
+ private:
+  struct Impl;
+  Impl* impl_;
+};
+
 class Renderer { // RendererT, src/renderer/mod.rs:16-19
  public:
   virtual ~Renderer() {}
@@ -108,7 +123,8 @@ class WavefrontPathTracer : public Renderer { // ≙ PathTracer, src/renderer/pt
   WavefrontPathTracer(int32_t max_depth, PixelSampler sampler, BoxFilter filter) : max_depth_(max_depth), sampler_(sampler), filter_(filter) {}
   std::vector<float> render(DeviceScene& scene, const OutputConfig& config) override;
   uint64_t seed = 1; int32_t pool_size = 0; uint32_t flags = 0; int32_t rank = 0, world_size = 1;
-  SptStats last_stats{};
+  RankGroup* group = nullptr; // set = render this rank's tiles and gather the frame on rank 0 over NCCL
+  SptStats last_stats{}; double last_reduce_ms = 0.0;
 
  private:
   int32_t max_depth_; PixelSampler sampler_; BoxFilter filter_;

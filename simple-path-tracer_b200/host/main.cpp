@@ -6,9 +6,18 @@
 //   --renderer-type T   renderer arm to create (default pt_wavefront; the file's "pt" names the reference's CPU integrator)
 //   --base-path P       resolve relative obj_file / image_file / external JSON against P instead of the scene file
 //   --device N  --seed N  --pool N  --spp N (overrides the renderer file)
-//   --rank R --world-size W   render only the tiles rank R of W owns (one process per GPU)
+//   --gpus N            one process per GPU: forks N ranks (GPU r = rank r) that render interleaved tiles and gather the
+//                       frame on rank 0 with one ncclReduce; rank 0 writes the image
+//   --rank R --world-size W [--nccl-id FILE]   what --gpus passes to each rank; without --nccl-id the rank only renders
+//                       the tiles it owns (no gather)
+//   --frames N          render the frame N times (same seed) and report the last one: steady-state timing without the
+//                       first call's allocations and NCCL connection set-up
 //   --raw FILE          also write the linear f32 mean image (height*width*3, row 0 = top)
 //   --dump-desc FILE    write the flattened scene (no GPU needed) and exit
+#include <sys/wait.h>
+#include <unistd.h>
+
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -31,7 +40,8 @@ std::string ext_of(const std::string& path) { // loader/mod.rs:8-32 dispatches o
 int main(int argc, char** argv) {
   std::string scene_path, renderer_path, output, camera, base_path, dump, raw, renderer_type = "pt_wavefront";
   bool has_camera = false;
-  int width = 512, height = 512, device = 0, pool = 0, spp = 0, rank = 0, world = 1;
+  int width = 512, height = 512, device = -1, pool = 0, spp = 0, rank = 0, world = 1, gpus = 0, frames = 1;
+  std::string nccl_id;
   uint64_t seed = 1;
   for (int i = 1; i < argc; i++) {
     const std::string a = argv[i];
@@ -50,10 +60,38 @@ int main(int argc, char** argv) {
     else if (a == "--spp") spp = atoi(val().c_str());
     else if (a == "--rank") rank = atoi(val().c_str());
     else if (a == "--world-size") world = atoi(val().c_str());
+    else if (a == "--gpus") gpus = atoi(val().c_str());
+    else if (a == "--nccl-id") nccl_id = val();
+    else if (a == "--frames") frames = std::max(1, atoi(val().c_str()));
     else if (a == "--raw") raw = val();
     else if (a == "--dump-desc") dump = val();
     else { fprintf(stderr, "error: unknown argument '%s'\n", a.c_str()); return 2; }
   }
+  if (gpus > 1) { // launcher: one child process per GPU, same command line plus the rank arguments
+    const std::string id_file = "/tmp/spt_nccl_id." + std::to_string((long)getpid());
+    unlink(id_file.c_str());
+    std::vector<pid_t> kids;
+    for (int r = 0; r < gpus; r++) {
+      const pid_t pid = fork();
+      if (pid < 0) { perror("fork"); return 1; }
+      if (pid == 0) {
+        std::vector<std::string> args;
+        for (int i = 0; i < argc; i++) { if (std::string(argv[i]) == "--gpus") { i++; continue; } args.push_back(argv[i]); }
+        for (const std::string& x : {std::string("--rank"), std::to_string(r), std::string("--world-size"), std::to_string(gpus), std::string("--nccl-id"), id_file}) args.push_back(x);
+        std::vector<char*> av;
+        for (auto& x : args) av.push_back(&x[0]);
+        av.push_back(nullptr);
+        execv("/proc/self/exe", av.data());
+        perror("execv"); _exit(127);
+      }
+      kids.push_back(pid);
+    }
+    int rc = 0;
+    for (pid_t k : kids) { int st = 0; waitpid(k, &st, 0); if (!WIFEXITED(st) || WEXITSTATUS(st) != 0) rc = 1; }
+    unlink(id_file.c_str());
+    return rc;
+  }
+  if (device < 0) device = world > 1 && !nccl_id.empty() ? rank : 0;
   try {
     if (scene_path.empty()) throw HostError("--scene is required");
     const std::string sext = ext_of(scene_path);
@@ -71,18 +109,26 @@ int main(int argc, char** argv) {
     WavefrontPathTracer* wf = dynamic_cast<WavefrontPathTracer*>(renderer.get());
     if (wf) { wf->seed = seed; wf->pool_size = pool; wf->rank = rank; wf->world_size = world; }
     DeviceScene scene(fs, device);
+    std::unique_ptr<RankGroup> group;
+    if (world > 1 && !nccl_id.empty()) { group.reset(new RankGroup(rank, world, device, nccl_id)); if (wf) wf->group = group.get(); }
     OutputConfig oc; oc.width = width; oc.height = height; oc.output_filename = output; oc.used_camera_name = camera; oc.has_camera_name = has_camera;
-    const auto t0 = std::chrono::steady_clock::now();
-    const std::vector<float> mean = renderer->render(scene, oc);
-    const double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    std::vector<float> mean;
+    double wall = 0.0;
+    for (int f = 0; f < frames; f++) {
+      const auto t0 = std::chrono::steady_clock::now();
+      mean = renderer->render(scene, oc);
+      wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    }
+    if (group && rank != 0) return 0; // the frame and the report live on rank 0
     if (!raw.empty()) { std::ofstream fh(raw, std::ios::binary); fh.write((const char*)mean.data(), (std::streamsize)(mean.size() * 4)); }
     if (wf) {
       const SptStats& st = wf->last_stats;
       printf("{\"paths\": %llu, \"ext_rays\": %llu, \"shadow_rays\": %llu, \"probe_rays\": %llu, \"iterations\": %llu, \"kernel_launches\": %llu, "
-             "\"seconds_device\": %.6f, \"seconds_wall\": %.6f, \"mpaths_per_s\": %.3f}\n",
+             "\"seconds_device\": %.6f, \"seconds_wall\": %.6f, \"mpaths_per_s\": %.3f, \"world_size\": %d, \"reduce_ms\": %.3f, \"frame_mpaths_per_s_wall\": %.3f}\n",
              (unsigned long long)st.paths, (unsigned long long)st.ext_rays, (unsigned long long)st.shadow_rays, (unsigned long long)st.probe_rays,
              (unsigned long long)st.iterations, (unsigned long long)st.kernel_launches, st.seconds_total, wall,
-             st.seconds_total > 0 ? st.paths / st.seconds_total / 1e6 : 0.0);
+             st.seconds_total > 0 ? st.paths / st.seconds_total / 1e6 : 0.0, group ? world : 1, wf->last_reduce_ms,
+             (double)width * height * rc.sampler.spp / wall / 1e6);
     }
   } catch (const std::exception& e) {
     fprintf(stderr, "Error: %s\n", e.what());

@@ -37,9 +37,20 @@ std::vector<float> WavefrontPathTracer::render(DeviceScene& scene, const OutputC
   rd.tile_w = rd.tile_h = 0;
   rd.rank = rank; rd.world_size = world_size;
   rd.pool_size = pool_size; rd.flags = flags;
-  std::vector<float> mean((size_t)config.width * config.height * 3);
-  std::vector<uint8_t> rgb8((size_t)config.width * config.height * 3);
-  check(spt_render(scene.handle(), &rd, mean.data(), rgb8.data(), &last_stats), "spt_render");
+  const size_t n = (size_t)config.width * config.height * 3;
+  std::vector<float> mean;
+  std::vector<uint8_t> rgb8(n);
+  if (group) {
+    mean = group->render_and_gather(scene, rd, &last_stats, &last_reduce_ms);
+    if (group->rank != 0) return mean; // empty: the frame lives on rank 0
+    for (size_t i = 0; i < n; i++) { // Film::color_to_rgb, film.rs:94-99 (the library does this on the device for spt_render)
+      const float v = mean[i] * 255.0f;
+      rgb8[i] = (uint8_t)(v > 0.0f ? (v > 255.0f ? 255.0f : v) : 0.0f); // NaN -> 0, like the device conversion
+    }
+  } else {
+    mean.resize(n);
+    check(spt_render(scene.handle(), &rd, mean.data(), rgb8.data(), &last_stats), "spt_render");
+  }
   if (!config.output_filename.empty()) save_png(config.output_filename, config.width, config.height, rgb8.data());
   return mean;
 }

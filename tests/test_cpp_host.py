@@ -260,3 +260,36 @@ def test_cpp_host_render_equals_python_host_render(host_bin, tmp_path, ctx, name
     disk = np.asarray(Image.open(png).convert("RGB"))
     assert disk.shape == (96, 160, 3)
     assert (np.abs(disk.astype(int) - rgb8.astype(int)) <= 1).mean() > 0.995
+
+
+def _c1b_files(tmp_path, spp=8):
+    sj, rj = tmp_path / "s.json", tmp_path / "pt.json"
+    sj.write_text(json.dumps(scenes.c1b()))
+    rj.write_text(json.dumps(dict(scenes.PT_JSON, sampler={"type": "recurrence", "spp": spp})))
+    return sj, rj
+
+
+def test_cpp_host_rank_launcher_fails_loudly_without_gpus(host_bin, tmp_path):
+    if os.path.exists("/dev/nvidiactl"):
+        pytest.skip("this box has a GPU")
+    sj, rj = _c1b_files(tmp_path)
+    r = run_host(host_bin, ["--scene", str(sj), "--base-path", scenes.BASE_PATH, "--renderer", str(rj), "--output", str(tmp_path / "o.png"),
+                            "--gpus", "2"], check=False)
+    assert r.returncode == 1 and r.stderr.count("spt_context_create") == 2, r.stderr  # both ranks report, nothing is rendered
+
+
+@pytest.mark.gpu
+def test_cpp_host_two_ranks_over_nccl_equal_one_rank(host_bin, tmp_path):
+    """spt_host --gpus 2: two processes, interleaved tiles, one ncclReduce -> the very same frame as one process."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    sj, rj = _c1b_files(tmp_path)
+    common = ["--scene", str(sj), "--base-path", scenes.BASE_PATH, "--renderer", str(rj), "--width", "200", "--height", "120", "--seed", "5"]
+    run_host(host_bin, common + ["--output", str(tmp_path / "one.png"), "--raw", str(tmp_path / "one.f32")])
+    r = run_host(host_bin, common + ["--output", str(tmp_path / "two.png"), "--raw", str(tmp_path / "two.f32"), "--gpus", "2"])
+    st = json.loads(r.stdout.strip().splitlines()[-1])
+    assert st["world_size"] == 2 and 0 < st["paths"] < 200 * 120 * 8
+    one, two = np.fromfile(tmp_path / "one.f32", np.float32), np.fromfile(tmp_path / "two.f32", np.float32)
+    assert np.array_equal(one, two)
+    assert open(tmp_path / "one.png", "rb").read() == open(tmp_path / "two.png", "rb").read()
