@@ -293,3 +293,21 @@ def test_cpp_host_two_ranks_over_nccl_equal_one_rank(host_bin, tmp_path):
     one, two = np.fromfile(tmp_path / "one.f32", np.float32), np.fromfile(tmp_path / "two.f32", np.float32)
     assert np.array_equal(one, two)
     assert open(tmp_path / "one.png", "rb").read() == open(tmp_path / "two.png", "rb").read()
+
+
+@pytest.mark.parametrize("name", ["test_scene_00.json", "test_scene_01.json"])
+def test_both_hosts_load_the_reference_scene_files_verbatim(host_bin, tmp_path, name):
+    """The shipped scenes that need no image files (scenes/textures/ is not part of the reference checkout) go through both
+    loaders unchanged — external common_*.json sections, OBJ models and all — and flatten identically."""
+    path = os.path.join("/root/reference/scenes", name)
+    if not os.path.exists(path):
+        pytest.skip("reference checkout not present on this machine")
+    out = tmp_path / "ref.dump"
+    run_host(host_bin, ["--scene", path, "--dump-desc", str(out)])
+    got, want = read_dump(out), python_dump(loader.load_scene(path))
+    assert sorted(got) == sorted(want)
+    for k in want:
+        if k.endswith(".indices") or k in ("warnings", "misc"):
+            assert got[k] == want[k], k
+        else:
+            assert words_match(got[k], want[k]).all(), k
