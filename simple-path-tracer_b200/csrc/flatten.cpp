@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstring>
 #include <cfloat>
+#include <cstdlib>
 #include <algorithm>
 
 namespace spt {
@@ -171,6 +172,10 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
   std::vector<Box3> mesh_box(d.n_meshes);
   hs.meshes.resize(d.n_meshes);
   std::vector<std::vector<int>> blas_order(d.n_meshes);
+  // triangles per BLAS leaf (1..3).  Measured on C2 / C3 / C5: 2 beats 3 by 1.6-2.4 % whole-render (fewer triangle tests
+  // per ray outweigh the extra nodes); 1 equals 2 with more node memory.  SPT_BLAS_LEAF overrides it for experiments.
+  int blas_leaf = 2;
+  if (const char* e = getenv("SPT_BLAS_LEAF")) blas_leaf = std::max(1, std::min(3, atoi(e)));
   for (int mi = 0; mi < d.n_meshes; mi++) {
     const SptMeshDesc& m = d.meshes[mi];
     if (m.n_tris <= 0 || m.n_verts <= 0 || !m.position || !m.index) return bad("mesh: empty");
@@ -198,7 +203,7 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
     }
     hs.meshes[mi] = dm;
     // node/prim bases are patched below once the TLAS size is known: build with base 0 and offset afterwards
-    build_cwbvh(boxes, 3, 0, 0, blas_nodes[mi], blas_order[mi], &mesh_box[mi]);
+    build_cwbvh(boxes, blas_leaf, 0, 0, blas_nodes[mi], blas_order[mi], &mesh_box[mi]);
   }
   // ---- instances ------------------------------------------------------------------------------------------------------
   hs.inst.resize(d.n_instances); hs.inst_shade.resize(d.n_instances);

@@ -37,6 +37,9 @@ struct TravCounters { // only maintained by the COUNT instantiations
 #ifndef SPT_FETCH_STATIC
 #define SPT_FETCH_STATIC 0   // 1: chunks dealt round-robin to warps instead of a global atomic cursor
 #endif
+#ifndef SPT_NODE_PER_ROUND
+#define SPT_NODE_PER_ROUND 1
+#endif
 #ifndef SPT_FETCH_MIN_IDLE
 #define SPT_FETCH_MIN_IDLE 6 // refill the warp once this many lanes are without a ray
 #endif
@@ -370,7 +373,8 @@ SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCoun
     if (has && !fin && trav_has_leaf(T) && T.cur_inst < 0) fin = trav_inst<ANY, COUNT>(sc, T, st, cnt);
 #endif
     // ---- node step
-    {
+#pragma unroll
+    for (int k = 0; k < SPT_NODE_PER_ROUND; k++) {
       const bool p = has && !fin && trav_has_node(T) && !trav_has_leaf(T);
       if (COUNT) { const uint32_t m = __ballot_sync(FULL, p); cnt.node += p ? 1u : 0u; if (lane == 0 && m) cnt.w_node++; }
       if (p) trav_node<COUNT>(sc, T, st, cnt);

@@ -1,4 +1,4 @@
-for v in base pf0 pf2 base; do
+for v in base node2 base; do
   lib=""; [ $v != base ] && lib="--lib simple-path-tracer_b200/lib/variants/libspt_$v.so"
-  python tools/sweep.py c2:32 c4:8 c3:8 --tag $v $lib >> gpurun_out/r1_sweep_v14.log 2>&1
+  python tools/sweep.py c2:32 c5:2 c3:8 --tag $v $lib >> gpurun_out/r1_sweep_v16.log 2>&1
 done
