@@ -41,6 +41,7 @@ struct DrawSrc {
 struct PathRng {
   uint64_t state;
   SPT_HD float next() { return rng_uniform(state); }
+  SPT_HD void skip2() { state = state * 0x685f98a2018fade9ull + 0x1a08ee1184ba6d32ull; } // two LCG steps at once (A^2, (A+1)C)
 };
 
 // Sub-pixel offsets of the additive-recurrence (R2) sampler, pixel_sampler/recurrence.rs:41-56, in closed form:

@@ -14,6 +14,9 @@ struct PathRegs {
 };
 struct ShadowRay { float3 o, d, c; float tmin, tmax; bool emit; };
 
+#ifndef SPT_SHADE_DEFER_SAMPLE
+#define SPT_SHADE_DEFER_SAMPLE 1
+#endif
 #ifndef SPT_SHADE_PREFETCH
 #define SPT_SHADE_PREFETCH 0 // 0 off (default: measured neutral on C2/C3/C4), 1 prefetch.global.L2, 2 prefetch.global.L1
 #endif
@@ -139,7 +142,12 @@ __global__ void __launch_bounds__(SPT_BLOCK, ShadeCfg<MAT>::min_blocks) k_shade(
     float3 po = g.p;
     const float3 wo = to_local(fr, -s.rd);
     BsdfSample bs;
-    bsdf_sample<MAT>(bsdf, wo, s.rng, bs);
+    // Lambert draws exactly two numbers for its sample: take a copy of the stream for them, step the path stream past
+    // them, and compute the sample AFTER next-event estimation, so that its 10 registers are not live across the light
+    // sampling code (same draws in the same order as sampling first; pt.rs:120-179).
+    PathRng rng_bs; rng_bs.state = s.rng.state;
+    if constexpr (MAT == 0 && SPT_SHADE_DEFER_SAMPLE) s.rng.skip2();
+    else bsdf_sample<MAT>(bsdf, wo, s.rng, bs);
     bool dead_after_nee = false;
     if constexpr (PROBE) {
       if (bs.need_probe) { // Subsurface::sample, substrate.rs:231-333
@@ -200,6 +208,10 @@ __global__ void __launch_bounds__(SPT_BLOCK, ShadeCfg<MAT>::min_blocks) k_shade(
         sh.emit = true; sh.o = po; sh.d = ls.dir; sh.tmin = 1e-4f / fmaxf(fabsf(wi.z), 0.00001f); sh.tmax = ls.dist - 0.001f; sh.c = s.thr * li;
       }
     }
+    if constexpr (MAT == 0 && SPT_SHADE_DEFER_SAMPLE) {
+      push_shadow(P, sh, s.pixel, n_culled);
+      bsdf_sample<MAT>(bsdf, wo, rng_bs, bs);
+    }
     if (dead_after_nee) terminate = true;
     else {
       s.last_pdf = bs.pdf;
@@ -210,7 +222,7 @@ __global__ void __launch_bounds__(SPT_BLOCK, ShadeCfg<MAT>::min_blocks) k_shade(
       if (!(bs.dir == DIR_REFLECT ? hd >= 0.f : hd <= 0.f)) terminate = true;
       else if (dot3(wi_world, g.n) < 0.f) s.medium = sf.double_sided ? -1 : sf.inside_medium; // pt.rs:190-192, surface.rs:105-111
     }
-    push_shadow(P, sh, s.pixel, n_culled);
+    if constexpr (!(MAT == 0 && SPT_SHADE_DEFER_SAMPLE)) push_shadow(P, sh, s.pixel, n_culled);
     finish_bounce(P, slot, s, terminate);
   }
   warp_sum_to(&P.ctr->nonfinite, nonfinite);
