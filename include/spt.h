@@ -264,6 +264,9 @@ typedef struct SptStats {
 typedef struct SptSceneInfo {
   int64_t tlas_nodes, blas_nodes, triangles, instances;
   int64_t bytes_nodes, bytes_tris, bytes_total;
+  double seconds_bvh;     /* acceleration-structure build inside spt_scene_create (all BLASes + TLAS) */
+  double seconds_create;  /* whole spt_scene_create: flatten + build + upload */
+  int64_t blas_on_device; /* how many BLASes were built by the GPU builder (big meshes) rather than the host SAH builder */
 } SptSceneInfo;
 
 typedef struct SptContext SptContext;

@@ -1,6 +1,7 @@
 // bvh_build.h — host-side compressed wide BVH builder (see bvh_build.cpp).
 #pragma once
 #include <stdint.h>
+#include <string>
 #include <vector>
 
 namespace spt {
@@ -23,5 +24,10 @@ static_assert(sizeof(CwNode) == 80, "CwNode must be 80 bytes");
 // prim_boxes of the i-th primitive in leaf order.  max_leaf in 1..3 (primitives per leaf slot).
 void build_cwbvh(const std::vector<Box3>& prim_boxes, int max_leaf, uint32_t node_base, uint32_t prim_base,
                  std::vector<CwNode>& out_nodes, std::vector<int>& out_prim_order, Box3* root_box);
+
+// The same structure built on the current CUDA device (bvh_build_gpu.cu: Morton sort -> radix tree -> refit -> wide
+// collapse); node and primitive bases are 0.  Needs >= 2 primitives.  Returns false with *err set on a CUDA failure.
+bool build_cwbvh_device(const std::vector<Box3>& prim_boxes, int max_leaf, std::vector<CwNode>& out_nodes, std::vector<int>& out_prim_order,
+                        Box3* root_box, std::string* err);
 
 } // namespace spt

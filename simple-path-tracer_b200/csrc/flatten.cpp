@@ -7,6 +7,8 @@
 #include <cmath>
 #include <cstring>
 #include <cfloat>
+#include <chrono>
+#include <string>
 #include <cstdlib>
 #include <algorithm>
 
@@ -176,6 +178,10 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
   // per ray outweigh the extra nodes); 1 equals 2 with more node memory.  SPT_BLAS_LEAF overrides it for experiments.
   int blas_leaf = 2;
   if (const char* e = getenv("SPT_BLAS_LEAF")) blas_leaf = std::max(1, std::min(3, atoi(e)));
+  // BLAS builder: meshes of >= SPT_DEVICE_BUILD_MIN_TRIS triangles are built on the GPU (LBVH, ~100x faster to build, a few
+  // per cent slower to trace), smaller ones with the host SAH builder.  SPT_BVH_BUILD=host|device forces one of them.
+  int bvh_mode = 1;
+  if (const char* e = getenv("SPT_BVH_BUILD")) bvh_mode = !strcmp(e, "host") ? 0 : (!strcmp(e, "device") ? 2 : 1);
   for (int mi = 0; mi < d.n_meshes; mi++) {
     const SptMeshDesc& m = d.meshes[mi];
     if (m.n_tris <= 0 || m.n_verts <= 0 || !m.position || !m.index) return bad("mesh: empty");
@@ -203,7 +209,14 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
     }
     hs.meshes[mi] = dm;
     // node/prim bases are patched below once the TLAS size is known: build with base 0 and offset afterwards
-    build_cwbvh(boxes, blas_leaf, 0, 0, blas_nodes[mi], blas_order[mi], &mesh_box[mi]);
+    const bool on_device = bvh_mode == 2 || (bvh_mode == 1 && m.n_tris >= SPT_DEVICE_BUILD_MIN_TRIS);
+    const auto tb0 = std::chrono::steady_clock::now();
+    if (on_device && m.n_tris >= 2) {
+      std::string berr;
+      if (!build_cwbvh_device(boxes, blas_leaf, blas_nodes[mi], blas_order[mi], &mesh_box[mi], &berr)) return bad(berr.c_str());
+      hs.blas_on_device++;
+    } else build_cwbvh(boxes, blas_leaf, 0, 0, blas_nodes[mi], blas_order[mi], &mesh_box[mi]);
+    hs.seconds_bvh += std::chrono::duration<double>(std::chrono::steady_clock::now() - tb0).count();
   }
   // ---- instances ------------------------------------------------------------------------------------------------------
   hs.inst.resize(d.n_instances); hs.inst_shade.resize(d.n_instances);
@@ -244,7 +257,9 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
   // ---- TLAS, then lay the BLASes out behind it ---------------------------------------------------------------------------
   std::vector<uint32_t> mesh_tri_base(std::max(1, d.n_meshes), 0u);
   std::vector<CwNode> tlas; std::vector<int> tlas_order;
+  const auto tt0 = std::chrono::steady_clock::now();
   build_cwbvh(inst_box, 1, 0, 0, tlas, tlas_order, nullptr);
+  hs.seconds_bvh += std::chrono::duration<double>(std::chrono::steady_clock::now() - tt0).count();
   hs.nodes = tlas; hs.tlas_nodes = (int64_t)tlas.size();
   hs.tlas_inst.assign(tlas_order.begin(), tlas_order.end());
   for (int mi = 0; mi < d.n_meshes; mi++) {

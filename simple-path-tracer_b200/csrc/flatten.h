@@ -1,5 +1,8 @@
 // flatten.h — host-side flattening of an SptSceneDesc into the device arrays of scene.h.
 #pragma once
+#ifndef SPT_DEVICE_BUILD_MIN_TRIS
+#define SPT_DEVICE_BUILD_MIN_TRIS (1 << 18) // meshes at least this big get their BLAS built on the GPU
+#endif
 #include <string>
 #include <vector>
 #include "../../include/spt.h"
@@ -41,6 +44,8 @@ struct HostScene {
   int light_sampler = 0, env_light_index = -1;
   bool has_image_tex = false;
   int64_t tlas_nodes = 0, blas_nodes = 0;
+  double seconds_bvh = 0.0, seconds_create = 0.0; // build statistics (spt_scene_info)
+  int64_t blas_on_device = 0;
 };
 
 // Returns an empty string on success, else the error message.

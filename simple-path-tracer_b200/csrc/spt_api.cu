@@ -1,5 +1,6 @@
 // spt_api.cu — the extern "C" entry points of include/spt.h: context, scene upload, ray batches, render loop.
 #include <cstdio>
+#include <chrono>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -106,6 +107,7 @@ int32_t spt_scene_create(SptContext* ctx, const SptSceneDesc* desc, SptScene** o
   SptScene* s = new (std::nothrow) SptScene();
   if (!s) return fail(SPT_ERR_INVALID, "out of host memory");
   s->ctx = ctx;
+  const auto t_create = std::chrono::steady_clock::now();
   const std::string err = spt::flatten_scene(*desc, s->hs);
   if (!err.empty()) { delete s; return fail(SPT_ERR_INVALID, err); }
   spt::HostScene& h = s->hs;
@@ -142,6 +144,7 @@ int32_t spt_scene_create(SptContext* ctx, const SptSceneDesc* desc, SptScene** o
   for (int i = 0; i < 2; i++) CU(cudaEventCreateWithFlags(&s->ev_join[i], cudaEventDisableTiming));
   CU(cudaMalloc(&s->ctr, sizeof(DevCounters))); CU(cudaMalloc(&s->batch_next, sizeof(uint32_t)));
   CU(cudaMallocHost(&s->h_ctr, sizeof(DevCounters)));
+  s->hs.seconds_create = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_create).count();
   *out = s;
   return SPT_OK;
 }
@@ -163,6 +166,7 @@ int32_t spt_scene_info(const SptScene* s, SptSceneInfo* out) {
   out->bytes_nodes = (int64_t)(s->hs.nodes.size() * sizeof(spt::CwNode)); out->bytes_tris = (int64_t)(s->hs.tris.size() * sizeof(float4));
   int64_t t = 0; for (const DevBuf& b : s->bufs) t += (int64_t)b.bytes;
   out->bytes_total = t;
+  out->seconds_bvh = s->hs.seconds_bvh; out->seconds_create = s->hs.seconds_create; out->blas_on_device = s->hs.blas_on_device;
   return SPT_OK;
 }
 

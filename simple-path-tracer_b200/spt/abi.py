@@ -128,7 +128,8 @@ class Stats(C.Structure):
 class SceneInfo(C.Structure):
     _fields_ = [("tlas_nodes", C.c_int64), ("blas_nodes", C.c_int64), ("triangles", C.c_int64),
                 ("instances", C.c_int64), ("bytes_nodes", C.c_int64), ("bytes_tris", C.c_int64),
-                ("bytes_total", C.c_int64)]
+                ("bytes_total", C.c_int64), ("seconds_bvh", C.c_double), ("seconds_create", C.c_double),
+                ("blas_on_device", C.c_int64)]
 
 
 # every symbol include/spt.h declares (tests check the .so exports exactly these)
