@@ -277,8 +277,11 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
         P[c] = m.position + 3 * vi;
         N[c] = m.normal ? m.normal + 3 * vi : nz; UV[c] = m.texcoord ? m.texcoord + 2 * vi : uv0;
         T[c] = m.tangent ? m.tangent + 3 * vi : tx; B[c] = m.bitangent ? m.bitangent + 3 * vi : by;
-        hs.tris.push_back(make_float4(P[c][0], P[c][1], P[c][2], c == 0 ? idf : 0.f));
       }
+      // (p0, id), e1 = p1 - p0, e2 = p2 - p0: the two edge vectors Triangle::intersect_ray recomputes per test (triangle.rs:128-129)
+      // are stored instead of the vertices — same IEEE subtraction, done once here (this file is built with -ffp-contract=off)
+      hs.tris.push_back(make_float4(P[0][0], P[0][1], P[0][2], idf));
+      for (int c = 1; c < 3; c++) hs.tris.push_back(make_float4(P[c][0] - P[0][0], P[c][1] - P[0][1], P[c][2] - P[0][2], 0.f));
       // Triangle::pdf / BvhAccel::pdf: 1 / max(area, 1e-3) / n_tris (triangle.rs:272-280, bvh.rs:300-302, Q6)
       const V3 e1{P[1][0] - P[0][0], P[1][1] - P[0][1], P[1][2] - P[0][2]}, e2{P[2][0] - P[0][0], P[2][1] - P[0][1], P[2][2] - P[0][2]};
       const float area = length(cross(e1, e2)) * 0.5f;

@@ -6,7 +6,7 @@
 //              n0 = (p.x, p.y, p.z, [ex ey ez imask])         p = quantisation origin, e = per-axis exponent
 //              n1 = (child_base, prim_base, meta[0..3], meta[4..7])
 //              n2 = (qlo_x[0..7], qlo_y[0..7])  n3 = (qlo_z[0..7], qhi_x[0..7])  n4 = (qhi_y[0..7], qhi_z[0..7])
-//  tris    : 48 B = 3 x float4 per triangle in BLAS leaf order: (p0, tri_id) (p1, -) (p2, -)  — the reference's
+//  tris    : 48 B = 3 x float4 per triangle in BLAS leaf order: (p0, tri_id) (e1 = p1-p0, -) (e2 = p2-p0, -)  — the reference's
 //            Triangle (triangle.rs:23-27) reduced to what intersect_ray (:124-147) reads.
 //  shade_tris: 144 B = 9 x float4 per triangle in the SAME leaf order: the vertex attributes Triangle::intersect
 //            interpolates (triangle.rs:188-213), pre-gathered so shading a hit is one indexed fetch instead of the

@@ -111,8 +111,7 @@ SPT_D bool leaf_intersect(const DScene& sc, int inst, int tri, float3 o, float3 
     return false;
   }
   const float4* tp = sc.tris + 3 * (size_t)tri;
-  const float3 p0 = mk3(ldg4(tp)), p1 = mk3(ldg4(tp + 1)), p2 = mk3(ldg4(tp + 2));
-  const float3 e1 = xsub3(p1, p0), e2 = xsub3(p2, p0), q = xcross3(d, e2);
+  const float3 p0 = mk3(ldg4(tp)), e1 = mk3(ldg4(tp + 1)), e2 = mk3(ldg4(tp + 2)), q = xcross3(d, e2);
   float det = xdot3(e1, q);
   if (det == 0.0f) return false;
   det = __fdiv_rn(1.0f, det);
