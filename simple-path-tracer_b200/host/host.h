@@ -36,6 +36,7 @@ void calc_tangents(Mesh& m);
 struct Image8 { int width = 0, height = 0; std::vector<uint8_t> rgba; };
 Image8 load_png(const std::string& path);                                              // 8-bit, non-interlaced
 void save_png(const std::string& path, int width, int height, const uint8_t* rgb);     // RGB8
+std::vector<float> load_exr_rgb(const std::string& path, int& width, int& height);     // scanline EXR, none/rle/zips/zip
 
 // The flat, index-linked scene that becomes an SptSceneDesc (owner of every array the descriptor points into).
 struct FlatScene {

@@ -350,7 +350,10 @@ void load_environment(FlatScene& fs, Params& p) { // environment.rs:86-108
   int w = 1, h = 1;
   std::vector<float> rgb;
   if (ty == "color") { const auto c = p.get_float3("color"); rgb = {c[0], c[1], c[2]}; }
-  else if (ty == "exr") throw HostError("environment - EXR decoding is not available in this image (no exr reader); use type 'npy' or 'procedural_sky'");
+  else if (ty == "exr") { // environment.rs:95-98, core/loader.rs:374-390
+    const std::string path = p.get_file_path("exr_file");
+    try { rgb = load_exr_rgb(path, w, h); } catch (const HostError& e) { throw HostError(std::string("environment - can't read '") + path + "': " + e.what()); }
+  }
   else if (ty == "npy") { // extension: lat-long f32 array [H,W,3]
     std::vector<size_t> shape;
     rgb = load_npy_f32(p.get_file_path("npy_file"), shape);

@@ -493,8 +493,13 @@ def _load_environment(fs, p):  # environment.rs:86-108
     scale = p.get_float3_or("scale", [1.0, 1.0, 1.0])
     if ty == "color":
         rgb = np.asarray(p.get_float3("color"), f32).reshape(1, 1, 3)
-    elif ty == "exr":
-        raise SceneError("environment - EXR decoding is not available in this image (no exr reader); use type 'npy' or 'procedural_sky'")
+    elif ty == "exr":  # environment.rs:95-98, core/loader.rs:374-390
+        from . import exrio
+        path = p.get_file_path("exr_file")
+        try:
+            rgb = exrio.read_exr(path)
+        except (OSError, exrio.ExrError) as e:
+            raise SceneError(f"environment - can't read '{path}': {e}")
     elif ty == "npy":  # extension: lat-long f32 array [H,W,3]
         rgb = np.load(p.get_file_path("npy_file")).astype(f32)
     elif ty == "procedural_sky":  # extension: see procedural_sky()

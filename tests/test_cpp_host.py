@@ -311,3 +311,47 @@ def test_both_hosts_load_the_reference_scene_files_verbatim(host_bin, tmp_path, 
             assert got[k] == want[k], k
         else:
             assert words_match(got[k], want[k]).all(), k
+
+
+EXR_FILES = [f"env_{c}_{t}.exr" for c in ("none", "rle", "zips", "zip") for t in ("float", "half")]
+
+
+@pytest.mark.parametrize("fname", EXR_FILES)
+def test_exr_environment_through_both_hosts(host_bin, tmp_path, fname):
+    """environment type "exr" (environment.rs:95-98): fixtures written by OpenCV's OpenEXR codec (tools/make_golden_exr.py)
+    decode to the committed source array bit for bit in spt/exrio.py and in host/exr.cpp."""
+    import shutil
+    golden = os.path.join(ROOT, "tests", "golden")
+    src = np.load(os.path.join(golden, "env_golden.npy"))
+    shutil.copy(os.path.join(golden, fname), tmp_path / fname)
+    sd = json.loads(json.dumps(scenes.c1()))
+    sd["environment"] = {"type": "exr", "exr_file": fname, "scale": [0.5, 1.0, 2.0]}
+    sj = tmp_path / "scene.json"
+    sj.write_text(json.dumps(sd))
+    fs = loader.load_scene(str(sj))
+    assert fs.env["width"] == 24 and fs.env["height"] == 12 and np.array_equal(fs.env["rgb"], src)
+    assert fs.env_light_index == 1 and sum(l["tag"] == abi.LIGHT["env"] for l in fs.lights) == 1  # Q8
+    out = tmp_path / "scene.dump"
+    run_host(host_bin, ["--scene", str(sj), "--dump-desc", str(out)])
+    got = read_dump(out)
+    assert got["env.rgb"] == src.tobytes() and got["env.size"] == struct.pack("<ii", 24, 12)
+    assert got["env.scale"] == np.asarray([0.5, 1.0, 2.0], np.float32).tobytes()
+
+
+def test_exr_unsupported_compression_is_reported(host_bin, tmp_path):
+    import shutil
+    shutil.copy(os.path.join(ROOT, "tests", "golden", "env_piz_half.exr"), tmp_path / "e.exr")
+    sd = json.loads(json.dumps(scenes.c1()))
+    sd["environment"] = {"type": "exr", "exr_file": "e.exr"}
+    sj = tmp_path / "scene.json"
+    sj.write_text(json.dumps(sd))
+    with pytest.raises(loader.SceneError, match="compression 'piz' is not supported"):
+        loader.load_scene(str(sj))
+    r = run_host(host_bin, ["--scene", str(sj), "--dump-desc", str(tmp_path / "x")], check=False)
+    assert r.returncode == 1 and "compression 'piz' is not supported" in r.stderr
+    sd["environment"]["exr_file"] = "missing.exr"
+    sj.write_text(json.dumps(sd))
+    with pytest.raises(loader.SceneError, match="can't read"):
+        loader.load_scene(str(sj))
+    r = run_host(host_bin, ["--scene", str(sj), "--dump-desc", str(tmp_path / "x")], check=False)
+    assert r.returncode == 1 and "can't read" in r.stderr
