@@ -222,6 +222,8 @@ typedef struct SptBxdfResult {
 #define SPT_RENDER_NO_SORT 2u         /* disable material binning of the shade stage (for A/B timing) */
 #define SPT_RENDER_TIME_STAGES 4u     /* fill seconds_stage[] from CUDA events around every kernel launch (implies SERIAL) */
 #define SPT_RENDER_SERIAL 8u          /* issue every kernel on one stream (default: independent kernels of an iteration overlap) */
+#define SPT_RENDER_ACCUMULATE 16u     /* progressive rendering: keep the film of the previous call on this scene (same width x height)
+                                         and add this call's samples to it; the outputs are the mean over all samples so far */
 
 /* Default screen tile = the 8x4 pixel block one warp generates camera samples for.  Measured on C2 at 8 ranks: per-rank
  * render times spread by 8 % with 32x32 tiles (255 tiles per rank), by 1.3 % with 8x4 (8100 per rank). */
@@ -241,6 +243,10 @@ typedef struct SptRenderDesc { /* OutputConfig (renderer/mod.rs:9-14) + PathTrac
   int32_t rank, world_size;/* this process renders the tiles it owns; others stay 0 */
   int32_t pool_size;       /* resident path slots (0 = default: 2^22, fewer for small renders) */
   uint32_t flags;
+  int32_t spp_first, spp_count; /* render only the samples [spp_first, spp_first + spp_count) of every pixel's spp (0, 0 = all).
+                                   Sample k of a pixel is the same path whichever call renders it (streams and sampler offsets are
+                                   keyed by the sample index), so passes over consecutive ranges with SPT_RENDER_ACCUMULATE add up,
+                                   bit for bit, to the frame rendered in one call — also across a spt_film_save / spt_film_load. */
 } SptRenderDesc;
 
 typedef struct SptStats {
@@ -309,6 +315,12 @@ int32_t spt_render(SptScene* scene, const SptRenderDesc* desc, float* out_rgb_me
 /* Same, result left in device memory (width*height*3 f32; pixels of other ranks are 0) so the
  * host can reduce it over NCCL without a round trip. */
 int32_t spt_render_device(SptScene* scene, const SptRenderDesc* desc, float* d_rgb_mean, SptStats* stats);
+
+/* Progressive dump / resume: the film is 3 x int64 per pixel (sums in 2^-24 fixed point), row 0 = top.  spt_film_save copies the
+ * film of the last render on this scene to the host (n_values = width*height*3); spt_film_load installs one as if `spp_done`
+ * samples per pixel had been accumulated, so the next SPT_RENDER_ACCUMULATE call continues from it. */
+int32_t spt_film_save(SptScene* scene, int64_t* out_values, int64_t n_values);
+int32_t spt_film_load(SptScene* scene, const int64_t* values, int32_t width, int32_t height, int32_t spp_done);
 
 /* Host-only helper (no device needed): the ids of the screen tiles rank `rank` of `world_size` owns for a
  * width x height image cut into tile_w x tile_h tiles (0 = the default).  Tiles are dealt round-robin in hash order, so

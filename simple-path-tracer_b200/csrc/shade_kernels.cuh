@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(SPT_BLOCK, ShadeCfg<MAT>::min_blocks) k_shade(
       const uint32_t k = s.sample;
       PathRng r2; r2.state = rng_init(P.seed, s.pixel, k);
       float ox, oy, x, y; pixel_offset(P, s.pixel, k, r2, ox, oy); film_xy(P, s.pixel, ox, oy, x, y);
-      const float aspect = (float)P.width / (float)P.height, ssi = 1.0f / sqrtf((float)P.spp);
+      const float aspect = (float)P.width / (float)P.height, ssi = 1.0f / sqrtf((float)P.spp_frame);
       const float3 eye = mk3(sc.camera.eye[0], sc.camera.eye[1], sc.camera.eye[2]);
       calc_differential(g, eye, camera_dir(sc.camera, x + aspect / (float)P.width * ssi, y), eye, camera_dir(sc.camera, x, y + ssi / (float)P.height));
     }

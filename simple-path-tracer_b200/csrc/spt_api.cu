@@ -36,7 +36,8 @@ struct SptScene {
   std::vector<DCamera> cameras;
   // render-time buffers, grown on demand and reused across spt_render calls
   void* pool_mem = nullptr; size_t pool_bytes = 0; int pool_n = 0;
-  long long* film = nullptr; size_t film_px = 0;
+  long long* film = nullptr; size_t film_px = 0; // film_px = allocated pixels
+  int film_w = 0, film_h = 0, film_spp = 0;       // what the film currently holds: frame size and samples per pixel accumulated
   DevCounters* ctr = nullptr; uint32_t* batch_next = nullptr;
   uint32_t* tiles = nullptr; size_t tiles_cap = 0, n_tiles = 0; int tile_key[6] = {0, 0, 0, 0, 0, 0};
   float* out_mean = nullptr; uint8_t* out_rgb8 = nullptr; size_t out_px = 0;
@@ -293,12 +294,18 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   const int spp = r->sampler_kind == SPT_SAMPLER_JITTERED ? std::max(1, r->div_x) * std::max(1, r->div_y) : std::max(1, r->spp);
   const int tw = r->tile_w > 0 ? r->tile_w : SPT_DEFAULT_TILE_W, th = r->tile_h > 0 ? r->tile_h : SPT_DEFAULT_TILE_H;
   if (tw % 8 || th % 4) return fail(SPT_ERR_INVALID, "spt_render: tile_w must be a multiple of 8 and tile_h of 4");
+  // sample range of this call (progressive passes): [spp_first, spp_first + spp_pass) of the frame's spp
+  const int spp_first = r->spp_count > 0 ? r->spp_first : 0, spp_pass = r->spp_count > 0 ? r->spp_count : spp;
+  if (spp_first < 0 || spp_first + spp_pass > spp) return fail(SPT_ERR_INVALID, "spt_render: spp_first + spp_count exceeds the frame's spp");
+  const bool accumulate = (r->flags & SPT_RENDER_ACCUMULATE) != 0 && s->film && s->film_w == r->width && s->film_h == r->height && s->film_spp > 0;
+  if ((r->flags & SPT_RENDER_ACCUMULATE) && !accumulate && spp_first > 0)
+    return fail(SPT_ERR_INVALID, "spt_render: SPT_RENDER_ACCUMULATE with spp_first > 0 needs the film of a previous pass of the same size (or spt_film_load)");
   CU(cudaSetDevice(s->ctx->device));
   cudaStream_t st = s->stream;
   const size_t n_px = (size_t)r->width * r->height;
   // ---- buffers
   // default pool: 2^22 slots (measured optimum on B200 for 1080p..4K frames), fewer for renders smaller than that
-  const unsigned long long all_samples = (unsigned long long)n_px * (unsigned long long)spp;
+  const unsigned long long all_samples = (unsigned long long)n_px * (unsigned long long)spp_pass;
   int pool_n = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 22, std::max<unsigned long long>(1ull << 16, all_samples));
   pool_n = std::max(SPT_TRAV_BLOCK, (pool_n + SPT_TRAV_BLOCK - 1) / SPT_TRAV_BLOCK * SPT_TRAV_BLOCK);
   const size_t per_slot = sizeof(PathRec) + sizeof(float4) + 3 * sizeof(float4) + sizeof(int32_t) + sizeof(uint32_t) + SPT_NQ * sizeof(uint32_t);
@@ -307,7 +314,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
     CU(cudaMalloc(&s->pool_mem, per_slot * (size_t)pool_n));
     s->pool_n = pool_n; s->pool_bytes = per_slot * (size_t)pool_n;
   }
-  if (s->film_px < n_px) { cudaFree(s->film); s->film = nullptr; CU(cudaMalloc(&s->film, n_px * 3 * sizeof(long long))); s->film_px = n_px; }
+  if (s->film_px < n_px) { cudaFree(s->film); s->film = nullptr; s->film_spp = 0; CU(cudaMalloc(&s->film, n_px * 3 * sizeof(long long))); s->film_px = n_px; }
   RenderParams P; memset(&P, 0, sizeof(P));
   {
     char* p = (char*)s->pool_mem; const size_t N = (size_t)pool_n;
@@ -334,15 +341,16 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   }
   P.tiles = s->tiles; P.n_tiles = (int)s->n_tiles; P.tiles_x = tiles_x; P.tile_w = tw; P.tile_h = th;
   P.width = r->width; P.height = r->height; P.max_depth = r->max_depth;
-  P.sampler = r->sampler_kind; P.spp = spp; P.div_x = std::max(1, r->div_x); P.div_y = std::max(1, r->div_y);
+  P.sampler = r->sampler_kind; P.spp = spp_pass; P.spp_first = spp_first; P.spp_frame = spp; P.div_x = std::max(1, r->div_x); P.div_y = std::max(1, r->div_y);
   P.seed = r->seed;
   P.sort_materials = (r->flags & SPT_RENDER_NO_SORT) ? 0 : 1;
-  P.total_samples = (unsigned long long)s->n_tiles * (unsigned long long)(tw * th) * (unsigned long long)spp;
+  P.total_samples = (unsigned long long)s->n_tiles * (unsigned long long)(tw * th) * (unsigned long long)spp_pass;
   DScene ds = s->ds;
   ds.camera = s->cameras[r->camera_index];
   const bool count = (r->flags & SPT_RENDER_COUNT_TRAVERSAL) != 0;
   // ---- run
-  CU(cudaMemsetAsync(s->film, 0, n_px * 3 * sizeof(long long), st));
+  if (!accumulate) { CU(cudaMemsetAsync(s->film, 0, n_px * 3 * sizeof(long long), st)); s->film_spp = 0; }
+  s->film_w = r->width; s->film_h = r->height; s->film_spp += spp_pass;
   CU(cudaMemsetAsync(s->ctr, 0, sizeof(DevCounters), st));
   CU(cudaMemsetAsync(P.pool.flags, 0, (size_t)pool_n * sizeof(uint32_t), st));
   CU(cudaMemsetAsync(P.pool.hit_inst, 0xff, (size_t)pool_n * sizeof(int32_t), st));
@@ -435,7 +443,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
       if (s->h_ctr->it.live == 0) break;
     }
   }
-  spt::launch_resolve(s->film, (int)n_px, 1.0f / (float)spp, d_mean, d_rgb8, grid_for(s->ctx, (long long)n_px * 3, 8), st);
+  spt::launch_resolve(s->film, (int)n_px, 1.0f / (float)s->film_spp, d_mean, d_rgb8, grid_for(s->ctx, (long long)n_px * 3, 8), st);
   launches++;
   CU(cudaEventRecord(s->ev[1], st));
   CU(cudaMemcpyAsync(s->h_ctr, s->ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, st));
@@ -455,6 +463,26 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
 }
 
 } // namespace
+
+extern "C" int32_t spt_film_save(SptScene* s, int64_t* out_values, int64_t n_values) {
+  if (!s || !out_values) return fail(SPT_ERR_INVALID, "spt_film_save: null argument");
+  if (!s->film || s->film_spp <= 0) return fail(SPT_ERR_INVALID, "spt_film_save: no film (render first)");
+  if (n_values != (int64_t)s->film_w * s->film_h * 3) return fail(SPT_ERR_INVALID, "spt_film_save: n_values must be width*height*3 of the last render");
+  CU(cudaSetDevice(s->ctx->device));
+  CU(cudaMemcpy(out_values, s->film, (size_t)n_values * sizeof(long long), cudaMemcpyDeviceToHost));
+  return SPT_OK;
+}
+
+extern "C" int32_t spt_film_load(SptScene* s, const int64_t* values, int32_t width, int32_t height, int32_t spp_done) {
+  if (!s || !values) return fail(SPT_ERR_INVALID, "spt_film_load: null argument");
+  if (width <= 0 || height <= 0 || spp_done <= 0) return fail(SPT_ERR_INVALID, "spt_film_load: bad width/height/spp_done");
+  CU(cudaSetDevice(s->ctx->device));
+  const size_t n_px = (size_t)width * height;
+  if (s->film_px < n_px) { cudaFree(s->film); s->film = nullptr; s->film_spp = 0; CU(cudaMalloc(&s->film, n_px * 3 * sizeof(long long))); s->film_px = n_px; }
+  CU(cudaMemcpy(s->film, values, n_px * 3 * sizeof(long long), cudaMemcpyHostToDevice));
+  s->film_w = width; s->film_h = height; s->film_spp = spp_done;
+  return SPT_OK;
+}
 
 extern "C" int32_t spt_render_device(SptScene* s, const SptRenderDesc* r, float* d_rgb_mean, SptStats* stats) {
   return render_impl(s, r, d_rgb_mean, nullptr, stats);

@@ -67,7 +67,7 @@ SPT_D bool ordinal_to_sample(const RenderParams& P, unsigned long long s, uint32
   const unsigned long long per_tile = (unsigned long long)tp * (unsigned long long)P.spp;
   const uint32_t tl = (uint32_t)(s / per_tile);
   const uint32_t rem = (uint32_t)(s % per_tile);
-  k = rem / tp;
+  k = (uint32_t)P.spp_first + rem / tp;
   const uint32_t q = rem % tp, blk = q >> 5, l = q & 31u, bpr = (uint32_t)P.tile_w >> 3;
   const uint32_t tx = (blk % bpr) * 8u + (l & 7u), ty = (blk / bpr) * 4u + (l >> 3);
   const uint32_t tile = P.tiles[tl];
@@ -79,7 +79,7 @@ SPT_D bool ordinal_to_sample(const RenderParams& P, unsigned long long s, uint32
 // PixelSamplerT::next_sample in closed form (recurrence.rs:41-56, random.rs:31-38, jittered.rs:44-57 with Q16 fixed)
 template <class RNG>
 SPT_D void pixel_offset(const RenderParams& P, uint32_t pixel, uint32_t k, RNG& rng, float& ox, float& oy) {
-  if (P.sampler == 2) r2_offset((uint32_t)((unsigned long long)pixel * (unsigned long long)P.spp + k) + 1u, ox, oy);
+  if (P.sampler == 2) r2_offset((uint32_t)((unsigned long long)pixel * (unsigned long long)P.spp_frame + k) + 1u, ox, oy);
   else if (P.sampler == 0) { ox = rng.next(); oy = rng.next(); }
   else {
     const uint32_t ix = k % (uint32_t)P.div_x, iy = k / (uint32_t)P.div_x;

@@ -46,7 +46,8 @@ struct RenderParams {
   const uint32_t* tiles; // owned tile ids
   int32_t n_tiles, tiles_x, tile_w, tile_h;
   int32_t width, height, max_depth;
-  int32_t sampler, spp, div_x, div_y;
+  int32_t sampler, spp, div_x, div_y; // spp = samples per pixel rendered by THIS call
+  int32_t spp_first, spp_frame;       // index of its first sample; samples per pixel of the whole frame (sampler ordinals)
   int32_t sort_materials; // 0: every surface hit goes to the generic queue (SPT_RENDER_NO_SORT)
   uint64_t seed;
   unsigned long long total_samples; // n_tiles * tile_w * tile_h * spp

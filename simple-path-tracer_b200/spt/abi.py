@@ -24,6 +24,7 @@ RENDER_COUNT_TRAVERSAL = 1
 RENDER_NO_SORT = 2
 RENDER_TIME_STAGES = 4
 RENDER_SERIAL = 8
+RENDER_ACCUMULATE = 16
 
 
 class MeshDesc(C.Structure):
@@ -108,7 +109,8 @@ class RenderDesc(C.Structure):
     _fields_ = [("camera_index", C.c_int32), ("width", C.c_int32), ("height", C.c_int32), ("max_depth", C.c_int32),
                 ("sampler_kind", C.c_int32), ("spp", C.c_int32), ("div_x", C.c_int32), ("div_y", C.c_int32),
                 ("filter_radius", c_f), ("seed", C.c_uint64), ("tile_w", C.c_int32), ("tile_h", C.c_int32),
-                ("rank", C.c_int32), ("world_size", C.c_int32), ("pool_size", C.c_int32), ("flags", C.c_uint32)]
+                ("rank", C.c_int32), ("world_size", C.c_int32), ("pool_size", C.c_int32), ("flags", C.c_uint32),
+                ("spp_first", C.c_int32), ("spp_count", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -136,7 +138,7 @@ class SceneInfo(C.Structure):
 SYMBOLS = ["spt_last_error", "spt_version", "spt_context_create", "spt_context_destroy", "spt_scene_create",
            "spt_scene_upload", "spt_scene_info", "spt_scene_destroy", "spt_trace_batch", "spt_occluded_batch",
            "spt_trace_batch_device", "spt_occluded_batch_device", "spt_bxdf_batch", "spt_render",
-           "spt_render_device", "spt_owned_tiles"]
+           "spt_render_device", "spt_film_save", "spt_film_load", "spt_owned_tiles"]
 
 PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_PATH = os.path.join(PKG_ROOT, "lib", "libspt_cuda.so")
@@ -174,6 +176,8 @@ def load_library(path=None):
         "spt_bxdf_batch": [vp, vp, C.c_int64, vp],
         "spt_render": [vp, P(RenderDesc), vp, vp, P(Stats)],
         "spt_render_device": [vp, P(RenderDesc), vp, P(Stats)],
+        "spt_film_save": [vp, vp, C.c_int64],
+        "spt_film_load": [vp, vp, C.c_int32, C.c_int32, C.c_int32],
         "spt_owned_tiles": [C.c_int32] * 6 + [vp, C.c_int64, P(C.c_int64)],
     }
     for name, args in sig.items():

@@ -87,9 +87,9 @@ class Scene:
 
     # ---- seam B1
     def render_desc(self, width, height, spp=16, max_depth=8, sampler="recurrence", div=(1, 1), seed=1, camera=0,
-                    rank=0, world_size=1, pool_size=0, flags=0, tile=(0, 0), filter_radius=0.5):
+                    rank=0, world_size=1, pool_size=0, flags=0, tile=(0, 0), filter_radius=0.5, spp_range=(0, 0)):
         return abi.RenderDesc(camera, width, height, max_depth, abi.SAMPLER[sampler], spp, div[0], div[1], filter_radius,
-                              seed, tile[0], tile[1], rank, world_size, pool_size, flags)
+                              seed, tile[0], tile[1], rank, world_size, pool_size, flags, spp_range[0], spp_range[1])
 
     def render(self, width, height, want_rgb8=False, **kw):
         """spt_render: host buffers out.  Returns (mean image [H,W,3] f32, stats) or (mean, rgb8, stats)."""
@@ -100,6 +100,18 @@ class Scene:
         abi.check(self.lib, self.lib.spt_render(self.h, C.byref(rd), img.ctypes.data,
                                                 rgb8.ctypes.data if want_rgb8 else None, C.byref(st)))
         return (img, rgb8, st.as_dict()) if want_rgb8 else (img, st.as_dict())
+
+    # ---- progressive dump / resume
+    def film_save(self, width, height):
+        """spt_film_save: the int64 fixed-point film of the last render, [H,W,3]."""
+        out = np.zeros((height, width, 3), np.int64)
+        abi.check(self.lib, self.lib.spt_film_save(self.h, out.ctypes.data, out.size))
+        return out
+
+    def film_load(self, film, spp_done):
+        """spt_film_load: resume from a saved film that holds spp_done samples per pixel."""
+        film = np.ascontiguousarray(film, np.int64)
+        abi.check(self.lib, self.lib.spt_film_load(self.h, film.ctypes.data, film.shape[1], film.shape[0], spp_done))
 
     def render_device(self, d_out_ptr, width, height, **kw):
         """spt_render_device: result stays in device memory at d_out_ptr (width*height*3 f32)."""

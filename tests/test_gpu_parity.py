@@ -277,3 +277,39 @@ def test_device_built_bvh_is_interchangeable_with_the_host_built_one(ctx, monkey
     ib, _ = dev.render(160, 96, spp=8, seed=11)
     assert (np.abs(ia - ib).max(-1) <= 1e-6 * (np.abs(ia).max(-1) + 1e-3)).mean() > 0.999  # an equal-t tie may pick the other triangle
     host.close(); dev.close()
+
+
+@pytest.mark.parametrize("name, sampler, div", [("c2", "recurrence", (1, 1)), ("c4", "random", (1, 1)), ("c1b", "jittered", (4, 3))])
+def test_progressive_passes_and_film_resume_add_up_bit_for_bit(ctx, name, sampler, div):
+    """SPT_RENDER_ACCUMULATE + spp_first/spp_count: a frame rendered as passes over consecutive sample ranges — also with the
+    film saved, the scene destroyed and the film loaded into a fresh scene in between — equals the one-call frame exactly;
+    every intermediate output is the mean over the samples so far."""
+    from spt import abi, core, scenes
+    fs = scenes.load(name)
+    w, h = 176, 96
+    spp = div[0] * div[1] if sampler == "jittered" else 12
+    kw = dict(spp=spp, sampler=sampler, div=div, seed=21)
+    sc = core.Scene(ctx, fs)
+    full, st = sc.render(w, h, **kw)
+    film_full = sc.film_save(w, h)
+    a, sa = sc.render(w, h, spp_range=(0, 5), **kw)
+    assert sa["paths"] == w * h * 5
+    alone, _ = sc.render(w, h, spp=5, sampler=sampler, div=div, seed=21) if sampler == "random" else (None, None)
+    if alone is not None:
+        assert np.array_equal(a, alone)                       # the first 5 samples of 12 are the 5 samples of a 5-spp frame (random sampler)
+    film5 = sc.film_save(w, h)
+    b, sb = sc.render(w, h, spp_range=(5, 3), flags=abi.RENDER_ACCUMULATE, **kw)
+    film8 = sc.film_save(w, h)
+    assert np.array_equal(np.float32((film8.astype(np.float64) / 16777216.0).astype(np.float32) * np.float32(1.0 / 8)), b)
+    sc.close()
+    sc2 = core.Scene(ctx, fs)                                   # "another process": fresh scene, film from the checkpoint
+    with pytest.raises(abi.SptError, match="needs the film of a previous pass"):
+        sc2.render(w, h, spp_range=(8, spp - 8), flags=abi.RENDER_ACCUMULATE, **kw)
+    sc2.film_load(film8, 8)
+    c, sc_st = sc2.render(w, h, spp_range=(8, spp - 8), flags=abi.RENDER_ACCUMULATE, **kw)
+    assert np.array_equal(c, full) and np.array_equal(sc2.film_save(w, h), film_full)
+    assert sa["paths"] + sb["paths"] + sc_st["paths"] == st["paths"]
+    assert not np.array_equal(film5, film8)
+    with pytest.raises(abi.SptError, match="exceeds the frame's spp"):
+        sc2.render(w, h, spp_range=(spp - 1, 2), **kw)
+    sc2.close()
