@@ -125,6 +125,7 @@ class WavefrontPathTracer : public Renderer { // ≙ PathTracer, src/renderer/pt
   std::vector<float> render(DeviceScene& scene, const OutputConfig& config) override;
   uint64_t seed = 1; int32_t pool_size = 0; uint32_t flags = 0; int32_t rank = 0, world_size = 1;
   RankGroup* group = nullptr; // set = render this rank's tiles and gather the frame on rank 0 over NCCL
+  int32_t spp_first = 0, spp_count = 0; bool accumulate = false; // progressive passes (SptRenderDesc::spp_first / spp_count)
   SptStats last_stats{}; double last_reduce_ms = 0.0;
 
  private:

@@ -12,6 +12,10 @@
 //                       the tiles it owns (no gather)
 //   --frames N          render the frame N times (same seed) and report the last one: steady-state timing without the
 //                       first call's allocations and NCCL connection set-up
+//   --passes N          progressive rendering: the frame's spp in N passes over consecutive sample ranges (SPT_RENDER_ACCUMULATE);
+//                       the image file is rewritten after every pass
+//   --checkpoint FILE   after every pass, write the film (int64 fixed-point sums) + how many samples it holds
+//   --resume FILE       load such a checkpoint and render only the samples that are still missing
 //   --raw FILE          also write the linear f32 mean image (height*width*3, row 0 = top)
 //   --dump-desc FILE    write the flattened scene (no GPU needed) and exit
 #include <sys/wait.h>
@@ -40,7 +44,8 @@ std::string ext_of(const std::string& path) { // loader/mod.rs:8-32 dispatches o
 int main(int argc, char** argv) {
   std::string scene_path, renderer_path, output, camera, base_path, dump, raw, renderer_type = "pt_wavefront";
   bool has_camera = false;
-  int width = 512, height = 512, device = -1, pool = 0, spp = 0, rank = 0, world = 1, gpus = 0, frames = 1;
+  int width = 512, height = 512, device = -1, pool = 0, spp = 0, rank = 0, world = 1, gpus = 0, frames = 1, passes = 1;
+  std::string checkpoint, resume;
   std::string nccl_id;
   uint64_t seed = 1;
   for (int i = 1; i < argc; i++) {
@@ -63,6 +68,9 @@ int main(int argc, char** argv) {
     else if (a == "--gpus") gpus = atoi(val().c_str());
     else if (a == "--nccl-id") nccl_id = val();
     else if (a == "--frames") frames = std::max(1, atoi(val().c_str()));
+    else if (a == "--passes") passes = std::max(1, atoi(val().c_str()));
+    else if (a == "--checkpoint") checkpoint = val();
+    else if (a == "--resume") resume = val();
     else if (a == "--raw") raw = val();
     else if (a == "--dump-desc") dump = val();
     else { fprintf(stderr, "error: unknown argument '%s'\n", a.c_str()); return 2; }
@@ -114,6 +122,39 @@ int main(int argc, char** argv) {
     OutputConfig oc; oc.width = width; oc.height = height; oc.output_filename = output; oc.used_camera_name = camera; oc.has_camera_name = has_camera;
     std::vector<float> mean;
     double wall = 0.0;
+    if (wf && (passes > 1 || !resume.empty() || !checkpoint.empty())) {
+      if (group) throw HostError("--passes / --checkpoint / --resume are single-process options");
+      const int total = rc.sampler.kind == SPT_SAMPLER_JITTERED ? rc.sampler.division_x * rc.sampler.division_y : rc.sampler.spp;
+      int done = 0;
+      if (!resume.empty()) { // header: magic, width, height, spp_done; then width*height*3 int64
+        std::ifstream fh(resume, std::ios::binary);
+        int32_t hdr[4] = {0, 0, 0, 0};
+        if (!fh || !fh.read((char*)hdr, sizeof(hdr)) || hdr[0] != 0x46545053) throw HostError("'" + resume + "' is not a film checkpoint");
+        if (hdr[1] != width || hdr[2] != height || hdr[3] <= 0 || hdr[3] > total) throw HostError("checkpoint does not match --width/--height/spp");
+        std::vector<int64_t> film((size_t)width * height * 3);
+        if (!fh.read((char*)film.data(), (std::streamsize)(film.size() * 8))) throw HostError("truncated checkpoint");
+        if (spt_film_load(scene.handle(), film.data(), width, height, hdr[3]) != SPT_OK) throw HostError(std::string("spt_film_load: ") + spt_last_error());
+        done = hdr[3];
+      }
+      const int todo = total - done, per = (todo + passes - 1) / passes;
+      const auto t0 = std::chrono::steady_clock::now();
+      while (done < total) {
+        wf->spp_first = done; wf->spp_count = std::min(per, total - done); wf->accumulate = done > 0;
+        mean = renderer->render(scene, oc);
+        done += wf->spp_count;
+        if (!checkpoint.empty()) {
+          std::vector<int64_t> film((size_t)width * height * 3);
+          if (spt_film_save(scene.handle(), film.data(), (int64_t)film.size()) != SPT_OK) throw HostError(std::string("spt_film_save: ") + spt_last_error());
+          const int32_t hdr[4] = {0x46545053, width, height, done};
+          std::ofstream fh(checkpoint + ".tmp", std::ios::binary);
+          fh.write((const char*)hdr, sizeof(hdr)); fh.write((const char*)film.data(), (std::streamsize)(film.size() * 8));
+          fh.close();
+          if (!fh || rename((checkpoint + ".tmp").c_str(), checkpoint.c_str()) != 0) throw HostError("can't write '" + checkpoint + "'");
+        }
+        fprintf(stderr, "pass done: %d / %d spp\n", done, total);
+      }
+      wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    } else
     for (int f = 0; f < frames; f++) {
       const auto t0 = std::chrono::steady_clock::now();
       mean = renderer->render(scene, oc);

@@ -36,7 +36,8 @@ std::vector<float> WavefrontPathTracer::render(DeviceScene& scene, const OutputC
   rd.seed = seed;
   rd.tile_w = rd.tile_h = 0;
   rd.rank = rank; rd.world_size = world_size;
-  rd.pool_size = pool_size; rd.flags = flags;
+  rd.pool_size = pool_size; rd.flags = flags | (accumulate ? SPT_RENDER_ACCUMULATE : 0u);
+  rd.spp_first = spp_first; rd.spp_count = spp_count;
   const size_t n = (size_t)config.width * config.height * 3;
   std::vector<float> mean;
   std::vector<uint8_t> rgb8(n);

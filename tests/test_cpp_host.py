@@ -355,3 +355,33 @@ def test_exr_unsupported_compression_is_reported(host_bin, tmp_path):
         loader.load_scene(str(sj))
     r = run_host(host_bin, ["--scene", str(sj), "--dump-desc", str(tmp_path / "x")], check=False)
     assert r.returncode == 1 and "can't read" in r.stderr
+
+
+@pytest.mark.gpu
+def test_cpp_host_progressive_passes_checkpoint_and_resume(host_bin, tmp_path):
+    """--passes / --checkpoint / --resume of the compiled host: 3 passes, and 1 pass + a resumed run from its checkpoint, both
+    give the very image of the one-call render."""
+    sj, rj = _c1b_files(tmp_path, spp=9)
+    common = ["--scene", str(sj), "--base-path", scenes.BASE_PATH, "--renderer", str(rj), "--width", "120", "--height", "80", "--seed", "4"]
+    run_host(host_bin, common + ["--output", str(tmp_path / "one.png"), "--raw", str(tmp_path / "one.f32")])
+    run_host(host_bin, common + ["--output", str(tmp_path / "p3.png"), "--raw", str(tmp_path / "p3.f32"), "--passes", "3", "--checkpoint", str(tmp_path / "ck")])
+    one = np.fromfile(tmp_path / "one.f32", np.float32)
+    assert np.array_equal(one, np.fromfile(tmp_path / "p3.f32", np.float32))
+    hdr = np.fromfile(tmp_path / "ck", np.int32, 4)
+    assert hdr.tolist() == [0x46545053, 120, 80, 9]
+    # a run that stops after 4 of 9 samples (spp override), then a second process that resumes from its checkpoint
+    r4 = tmp_path / "pt4.json"
+    r4.write_text(json.dumps(dict(scenes.PT_JSON, sampler={"type": "random", "spp": 9})))
+    common_r = [x if x != str(rj) else str(r4) for x in common]
+    run_host(host_bin, common_r + ["--output", str(tmp_path / "full.png"), "--raw", str(tmp_path / "full.f32")])
+    # write a 4-sample checkpoint through the library, as a killed 9-spp run would have left it
+    from spt import abi, core
+    ctx = core.Context(0)
+    sc = core.Scene(ctx, loader.load_scene(scenes.c1b(), scenes.BASE_PATH))
+    sc.render(120, 80, spp=9, sampler="random", seed=4, spp_range=(0, 4))
+    film = sc.film_save(120, 80)
+    sc.close(); ctx.close()
+    with open(tmp_path / "ck4", "wb") as fh:
+        fh.write(np.asarray([0x46545053, 120, 80, 4], np.int32).tobytes()); fh.write(film.tobytes())
+    run_host(host_bin, common_r + ["--output", str(tmp_path / "res.png"), "--raw", str(tmp_path / "res.f32"), "--resume", str(tmp_path / "ck4")])
+    assert np.array_equal(np.fromfile(tmp_path / "full.f32", np.float32), np.fromfile(tmp_path / "res.f32", np.float32))
