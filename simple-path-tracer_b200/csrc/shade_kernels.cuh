@@ -92,7 +92,7 @@ template <int MAT> struct ShadeCfg { static constexpr int min_blocks = 4; }; // 
 template <int MAT, bool COUNT>
 __global__ void __launch_bounds__(SPT_BLOCK, ShadeCfg<MAT>::min_blocks) k_shade(const DScene sc, const RenderParams P) {
   constexpr bool PROBE = MAT < 0 || MAT == 7; // the BSSRDF probe ray needs the traversal stack
-  __shared__ uint2 s_stack[PROBE ? SPT_SSTACK : 1][PROBE ? SPT_TRAV_BLOCK : 1];
+  __shared__ uint2 s_stack[PROBE ? SPT_SSTACK + SPT_WSTASH : 1][PROBE ? SPT_TRAV_BLOCK : 1];
   uint32_t nonfinite = 0, n_probe = 0, n_culled = 0;
   TravCounters tc = {};
   constexpr int QI = MAT < 0 ? SPT_Q_GENERIC : MAT;

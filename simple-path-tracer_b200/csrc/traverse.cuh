@@ -33,6 +33,10 @@ struct TravCounters { // only maintained by the COUNT instantiations
 };
 
 #define SPT_SSTACK 16       // stack entries per thread in shared memory
+#ifndef SPT_WORLD_STASH
+#define SPT_WORLD_STASH 1   // 1: while a lane is inside a BLAS its world-space ray lives in shared memory, not in 10 registers
+#endif
+#define SPT_WSTASH (SPT_WORLD_STASH ? 5 : 0) // extra uint2 rows of the shared stack that hold the stashed world ray
 #define SPT_LSTACK 32       // overflow entries in local memory (untouched unless a ray goes deeper than SPT_SSTACK)
 #ifndef SPT_FETCH_STATIC
 #define SPT_FETCH_STATIC 0   // 1: chunks dealt round-robin to warps instead of a global atomic cursor
@@ -167,20 +171,41 @@ struct TravStack {
   uint2* lo;     // local-memory overflow
   SPT_D void push(int& sp, uint2 e) const { if (sp < SPT_SSTACK) sh[sp * SPT_TRAV_BLOCK] = e; else lo[sp - SPT_SSTACK] = e; sp++; }
   SPT_D uint2 pop(int& sp) const { --sp; return sp < SPT_SSTACK ? sh[sp * SPT_TRAV_BLOCK] : lo[sp - SPT_SSTACK]; }
+#if SPT_WORLD_STASH
+  SPT_D void stash(const RaySetup& r) const {
+    sh[(SPT_SSTACK + 0) * SPT_TRAV_BLOCK] = make_uint2(__float_as_uint(r.o.x), __float_as_uint(r.o.y));
+    sh[(SPT_SSTACK + 1) * SPT_TRAV_BLOCK] = make_uint2(__float_as_uint(r.o.z), __float_as_uint(r.d.x));
+    sh[(SPT_SSTACK + 2) * SPT_TRAV_BLOCK] = make_uint2(__float_as_uint(r.d.y), __float_as_uint(r.d.z));
+    sh[(SPT_SSTACK + 3) * SPT_TRAV_BLOCK] = make_uint2(__float_as_uint(r.idir.x), __float_as_uint(r.idir.y));
+    sh[(SPT_SSTACK + 4) * SPT_TRAV_BLOCK] = make_uint2(__float_as_uint(r.idir.z), r.octinv4);
+  }
+  SPT_D void unstash(RaySetup& r) const {
+    const uint2 a = sh[(SPT_SSTACK + 0) * SPT_TRAV_BLOCK], b = sh[(SPT_SSTACK + 1) * SPT_TRAV_BLOCK], c = sh[(SPT_SSTACK + 2) * SPT_TRAV_BLOCK],
+                d = sh[(SPT_SSTACK + 3) * SPT_TRAV_BLOCK], e = sh[(SPT_SSTACK + 4) * SPT_TRAV_BLOCK];
+    r.o = mk3(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(b.x));
+    r.d = mk3(__uint_as_float(b.y), __uint_as_float(c.x), __uint_as_float(c.y));
+    r.idir = mk3(__uint_as_float(d.x), __uint_as_float(d.y), __uint_as_float(e.x));
+    r.octinv4 = e.y;
+  }
+#endif
 };
 struct Trav {
-  float3 ow, dw; // the world-space ray (core/ray.rs); r holds the ray of the current space (world or object)
   float tmin;
-  RaySetup r;
+  RaySetup r;    // the ray of the current space: world (core/ray.rs) in the TLAS, object space inside a BLAS
+#if !SPT_WORLD_STASH
+  float3 ow, dw; // the world-space ray
   float3 widir; uint32_t woct; // idir / octant of the world-space ray, restored when a BLAS is left
+#endif
   HitRec hit;    // hit.t doubles as the running t_max (Intersection::t, intersection.rs:21-26)
   uint2 ng, tg;  // pending node group / primitive group of the current space (either may be empty)
   int sp, blas_base, cur_inst;
 };
 SPT_D void trav_begin(Trav& T, float3 o, float3 d, float tmin, float tmax) {
-  T.ow = o; T.dw = d; T.tmin = tmin;
+  T.tmin = tmin;
   ray_setup(T.r, o, d);
-  T.widir = T.r.idir; T.woct = T.r.octinv4;
+#if !SPT_WORLD_STASH
+  T.ow = o; T.dw = d; T.widir = T.r.idir; T.woct = T.r.octinv4;
+#endif
   T.hit.t = tmax; T.hit.u = T.hit.v = 0.f; T.hit.prim = -1; T.hit.inst = -1; T.hit.tri = -1; // Intersection::default
   T.ng = make_uint2(0u, 0x80000000u); T.tg = make_uint2(0u, 0u);
   T.sp = 0; T.blas_base = 0; T.cur_inst = -1;
@@ -234,7 +259,7 @@ SPT_D bool trav_inst(const DScene& sc, Trav& T, const TravStack& st, TravCounter
   const float4* ip = reinterpret_cast<const float4*>(sc.inst + iid);
   const float4 r0 = ldg4(ip), r1 = ldg4(ip + 1), r2 = ldg4(ip + 2), mt = ldg4(ip + 3);
   if (COUNT) cnt.insts++;
-  const float3 o2 = xmat_point(r0, r1, r2, T.ow), d2 = xmat_vec(r0, r1, r2, T.dw);
+  const float3 o2 = xmat_point(r0, r1, r2, T.r.o), d2 = xmat_vec(r0, r1, r2, T.r.d); // instances are only visited from the TLAS: r is the world ray
   const int kind = __float_as_int(mt.x), root = __float_as_int(mt.y);
   if (kind == 0) { // sphere
     if (COUNT) cnt.tris++;
@@ -265,6 +290,9 @@ SPT_D bool trav_inst(const DScene& sc, Trav& T, const TravStack& st, TravCounter
   if (T.tg.y != 0u) st.push(T.sp, T.tg);
   if (T.ng.y > 0x00ffffffu) st.push(T.sp, T.ng);
   T.blas_base = T.sp; T.cur_inst = iid;
+#if SPT_WORLD_STASH
+  st.stash(T.r);
+#endif
   if (kind & 2) { // small mesh: its triangles become the pending primitive group, no BLAS node step
     T.r.o = o2; T.r.d = d2;
     T.ng = make_uint2(0u, 0u);
@@ -279,7 +307,11 @@ SPT_D bool trav_inst(const DScene& sc, Trav& T, const TravStack& st, TravCounter
 // Called when neither a node nor a primitive group is pending: leave the BLAS if it is exhausted, pop the next group.
 // Returns true when the ray is finished.
 SPT_D bool trav_pop(Trav& T, const TravStack& st) {
+#if SPT_WORLD_STASH
+  if (T.cur_inst >= 0 && T.sp == T.blas_base) { T.cur_inst = -1; st.unstash(T.r); }
+#else
   if (T.cur_inst >= 0 && T.sp == T.blas_base) { T.cur_inst = -1; T.r.o = T.ow; T.r.d = T.dw; T.r.idir = T.widir; T.r.octinv4 = T.woct; }
+#endif
   if (T.sp == 0) return true;
   const uint2 e = st.pop(T.sp);
   if (e.y > 0x00ffffffu) { T.ng = e; T.tg = make_uint2(0u, 0u); } else { T.tg = e; T.ng = make_uint2(0u, 0u); }
@@ -331,7 +363,7 @@ SPT_D bool traverse(const DScene& sc, float3 ow, float3 dw, float tmin, HitRec& 
 #endif
 template <bool ANY, bool COUNT, class Src>
 SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCounters& cnt) {
-  __shared__ uint2 s_stack[SPT_SSTACK][SPT_TRAV_BLOCK];
+  __shared__ uint2 s_stack[SPT_SSTACK + SPT_WSTASH][SPT_TRAV_BLOCK];
   uint2 l_stack[SPT_LSTACK];
   TravStack st; st.sh = &s_stack[0][threadIdx.x]; st.lo = l_stack;
   const uint32_t total = src.total(), lane = threadIdx.x & 31u, FULL = 0xffffffffu;
