@@ -28,6 +28,6 @@ void build_cwbvh(const std::vector<Box3>& prim_boxes, int max_leaf, uint32_t nod
 // The same structure built on the current CUDA device (bvh_build_gpu.cu: Morton sort -> radix tree -> refit -> wide
 // collapse); node and primitive bases are 0.  Needs >= 2 primitives.  Returns false with *err set on a CUDA failure.
 bool build_cwbvh_device(const std::vector<Box3>& prim_boxes, int max_leaf, std::vector<CwNode>& out_nodes, std::vector<int>& out_prim_order,
-                        Box3* root_box, std::string* err);
+                        Box3* root_box, std::string* err, int algorithm = 1 /* 0 = LBVH (radix tree), 1 = PLOC */);
 
 } // namespace spt

@@ -3,9 +3,11 @@
 //
 //   1. 63-bit Morton codes of the primitive centroids                                k_morton
 //   2. radix sort of (code, primitive)                                               cub::DeviceRadixSort
-//   3. binary radix tree over the sorted codes (Karras, HPG 2012), one thread/node   k_radix_tree
-//   4. bottom-up box fit, second arrival at a node continues upward                  k_refit
-//   5. level-by-level collapse to 8-wide nodes (open the largest child until 8), octant-ordered slots, 8-bit quantised
+//   3. binary tree over the sorted primitives, either
+//        LBVH: radix tree (Karras, HPG 2012), one thread per node + bottom-up refit  k_radix_tree, k_refit
+//        PLOC: rounds of nearest-neighbour search in a Morton window + merge of mutual pairs + compaction
+//              (Meister & Bittner, TVCG 2018)                                        k_ploc_nn, k_ploc_merge, k_ploc_compact
+//   4. level-by-level collapse to 8-wide nodes (open the largest child until 8), octant-ordered slots, 8-bit quantised
 //      child boxes; nodes and primitive ranges are allocated with atomics           k_collapse
 //
 // The output has exactly the format of the host builder (bvh_build.cpp): same 80-byte nodes, inner children consecutive
@@ -16,6 +18,7 @@
 
 #include <cuda_runtime.h>
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 
 #include <cfloat>
 #include <cstdio>
@@ -57,7 +60,7 @@ __device__ __forceinline__ int delta(const uint64_t* __restrict__ keys, int n, i
 
 // Binary nodes: internal 0..n-2, leaf j = n-1+j.  Root = internal 0.
 __global__ void k_radix_tree(const uint64_t* __restrict__ keys, int n, int* __restrict__ left, int* __restrict__ right, int* __restrict__ parent,
-                             int* __restrict__ first, int* __restrict__ last) {
+                             int* __restrict__ count) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n - 1) return;
   const int d = delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1) >= 0 ? 1 : -1;
@@ -76,7 +79,7 @@ __global__ void k_radix_tree(const uint64_t* __restrict__ keys, int n, int* __re
   const int g = i + s * d + min(d, 0);
   const int lo = min(i, j), hi = max(i, j);
   const int lc = lo == g ? n - 1 + g : g, rc = hi == g + 1 ? n - 1 + g + 1 : g + 1;
-  left[i] = lc; right[i] = rc; first[i] = lo; last[i] = hi;
+  left[i] = lc; right[i] = rc; count[i] = hi - lo + 1;
   parent[lc] = i; parent[rc] = i;
   if (i == 0) parent[0] = -1;
 }
@@ -116,9 +119,69 @@ __global__ void k_refit(const Box3* __restrict__ prim_boxes, const uint32_t* __r
   }
 }
 
+
+// ---- PLOC: parallel locally-ordered clustering (Meister & Bittner, TVCG 2018) ---------------------------------------------
+// Clusters stay in Morton order.  Every round each cluster looks SPT_PLOC_RADIUS positions to either side for the neighbour
+// whose union with it has the smallest surface area; pairs that chose each other are merged into a new inner node, the rest
+// wait; a prefix sum compacts the survivors.  Near-SAH quality at a few times the cost of the radix tree.
+#ifndef SPT_PLOC_RADIUS
+#define SPT_PLOC_RADIUS 16
+#endif
+
+__global__ void k_ploc_init(const Box3* __restrict__ prim_boxes, const uint32_t* __restrict__ vals, int n, int* __restrict__ cid, Box3* __restrict__ cbox,
+                            Box3* __restrict__ nbox) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const Box3 b = prim_boxes[vals[j]];
+  cid[j] = n - 1 + j; cbox[j] = b; nbox[n - 1 + j] = b;
+}
+
+__global__ void k_ploc_nn(const Box3* __restrict__ cbox, int m, int* __restrict__ nn) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  const Box3 bi = cbox[i];
+  float best = FLT_MAX; int bj = -1;
+  const int j0 = max(0, i - SPT_PLOC_RADIUS), j1 = min(m - 1, i + SPT_PLOC_RADIUS);
+  for (int j = j0; j <= j1; j++) {
+    if (j == i) continue;
+    Box3 u = cbox[j];
+    box_union(u, bi);
+    const float a = box_area(u);
+    if (a < best) { best = a; bj = j; } // ties: the lower position wins on both sides of a pair, so mutual choices stay mutual
+  }
+  nn[i] = bj;
+}
+
+__global__ void k_ploc_merge(const int* __restrict__ cid, const Box3* __restrict__ cbox, int m, const int* __restrict__ nn, int* __restrict__ left,
+                             int* __restrict__ right, int* __restrict__ count, Box3* __restrict__ nbox, unsigned int* node_counter, int n,
+                             int* __restrict__ cid_tmp, Box3* __restrict__ cbox_tmp, int* __restrict__ valid) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  const int j = nn[i];
+  if (j >= 0 && nn[j] == i) {
+    if (i < j) {
+      const int id = (int)atomicAdd(node_counter, 1u);
+      const int a = cid[i], b = cid[j];
+      Box3 u = cbox[i];
+      box_union(u, cbox[j]);
+      left[id] = a; right[id] = b;
+      count[id] = (a >= n - 1 ? 1 : count[a]) + (b >= n - 1 ? 1 : count[b]);
+      nbox[id] = u;
+      cid_tmp[i] = id; cbox_tmp[i] = u; valid[i] = 1;
+    } else valid[i] = 0; // absorbed by its partner
+  } else { cid_tmp[i] = cid[i]; cbox_tmp[i] = cbox[i]; valid[i] = 1; }
+}
+
+__global__ void k_ploc_compact(const int* __restrict__ cid_tmp, const Box3* __restrict__ cbox_tmp, const int* __restrict__ valid, const int* __restrict__ pos,
+                               int m, int* __restrict__ cid, Box3* __restrict__ cbox) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m || !valid[i]) return;
+  cid[pos[i]] = cid_tmp[i]; cbox[pos[i]] = cbox_tmp[i];
+}
+
 struct CollapseArgs {
   int n, max_leaf;
-  const int *left, *right, *first, *last;
+  const int *left, *right, *count; // count[x] = primitives under inner node x
   const Box3* nbox;
   const uint32_t* vals;
   CwNode* nodes;
@@ -129,9 +192,19 @@ struct CollapseArgs {
   int n_in;
 };
 
-__device__ __forceinline__ bool is_leaf(const CollapseArgs& A, int x) { return x >= A.n - 1 || (A.last[x] - A.first[x] + 1) <= A.max_leaf; }
-__device__ __forceinline__ int leaf_count(const CollapseArgs& A, int x) { return x >= A.n - 1 ? 1 : A.last[x] - A.first[x] + 1; }
-__device__ __forceinline__ int leaf_first(const CollapseArgs& A, int x) { return x >= A.n - 1 ? x - (A.n - 1) : A.first[x]; }
+__device__ __forceinline__ bool is_leaf(const CollapseArgs& A, int x) { return x >= A.n - 1 || A.count[x] <= A.max_leaf; }
+__device__ __forceinline__ int leaf_count(const CollapseArgs& A, int x) { return x >= A.n - 1 ? 1 : A.count[x]; }
+// the (at most 3) primitives under a leaf-ified subtree, left to right
+__device__ __forceinline__ int leaf_prims(const CollapseArgs& A, int x, int out[3]) {
+  int stack[4], sp = 0, k = 0;
+  stack[sp++] = x;
+  while (sp > 0) {
+    const int y = stack[--sp];
+    if (y >= A.n - 1) { if (k < 3) out[k++] = (int)A.vals[y - (A.n - 1)]; }
+    else { stack[sp++] = A.right[y]; stack[sp++] = A.left[y]; }
+  }
+  return k;
+}
 
 __global__ void k_collapse(const CollapseArgs A) {
   const int w = blockIdx.x * blockDim.x + threadIdx.x;
@@ -220,10 +293,11 @@ __global__ void k_collapse(const CollapseArgs A) {
       A.items_out[item_base + r] = make_uint2((uint32_t)ch[c], child_base + r); // inner children: consecutive nodes in slot order
       r++;
     } else {
-      const int cnt = leaf_count(A, ch[c]), f0 = leaf_first(A, ch[c]);
+      int prims[3];
+      const int cnt = leaf_prims(A, ch[c], prims);
       const uint32_t unary = cnt == 1 ? 1u : (cnt == 2 ? 3u : 7u);
       cw.meta[s] = (uint8_t)((unary << 5) | po);
-      for (int i = 0; i < cnt; i++) A.order[prim_first + po + i] = (int)A.vals[f0 + i];
+      for (int i = 0; i < cnt; i++) A.order[prim_first + po + i] = prims[i];
       po += (uint32_t)cnt;
     }
   }
@@ -236,7 +310,7 @@ __global__ void k_collapse(const CollapseArgs A) {
 } // namespace
 
 bool build_cwbvh_device(const std::vector<Box3>& prim_boxes, int max_leaf, std::vector<CwNode>& out_nodes, std::vector<int>& out_prim_order,
-                        Box3* root_box, std::string* err) {
+                        Box3* root_box, std::string* err, int algorithm) {
   out_nodes.clear(); out_prim_order.clear();
   const int n = (int)prim_boxes.size();
   if (n < 2) { if (err) *err = "build_cwbvh_device: needs at least 2 primitives"; return false; }
@@ -250,14 +324,16 @@ bool build_cwbvh_device(const std::vector<Box3>& prim_boxes, int max_leaf, std::
   Box3 *d_boxes = nullptr, *d_nbox = nullptr;
   uint64_t *d_keys = nullptr, *d_keys2 = nullptr;
   uint32_t *d_vals = nullptr, *d_vals2 = nullptr;
-  int *d_left = nullptr, *d_right = nullptr, *d_parent = nullptr, *d_first = nullptr, *d_last = nullptr, *d_arrived = nullptr, *d_order = nullptr;
+  int *d_left = nullptr, *d_right = nullptr, *d_parent = nullptr, *d_count = nullptr, *d_arrived = nullptr, *d_order = nullptr;
+  int *d_cid[2] = {nullptr, nullptr}, *d_nn = nullptr, *d_valid = nullptr, *d_pos = nullptr;
+  Box3 *d_cbox[2] = {nullptr, nullptr};
   CwNode* d_nodes = nullptr;
   uint2 *d_items[2] = {nullptr, nullptr};
   unsigned int* d_ctr = nullptr; // node, prim, out
   void* d_tmp = nullptr;
   auto cleanup = [&]() {
     cudaFree(d_boxes); cudaFree(d_nbox); cudaFree(d_keys); cudaFree(d_keys2); cudaFree(d_vals); cudaFree(d_vals2); cudaFree(d_left); cudaFree(d_right);
-    cudaFree(d_parent); cudaFree(d_first); cudaFree(d_last); cudaFree(d_arrived); cudaFree(d_order); cudaFree(d_nodes); cudaFree(d_items[0]); cudaFree(d_items[1]);
+    cudaFree(d_parent); cudaFree(d_count); cudaFree(d_arrived); cudaFree(d_cid[0]); cudaFree(d_cid[1]); cudaFree(d_nn); cudaFree(d_valid); cudaFree(d_pos); cudaFree(d_cbox[0]); cudaFree(d_cbox[1]); cudaFree(d_order); cudaFree(d_nodes); cudaFree(d_items[0]); cudaFree(d_items[1]);
     cudaFree(d_ctr); cudaFree(d_tmp);
   };
   const size_t N = (size_t)n;
@@ -265,7 +341,7 @@ bool build_cwbvh_device(const std::vector<Box3>& prim_boxes, int max_leaf, std::
   BG_CU(cudaMalloc(&d_nbox, (2 * N - 1) * sizeof(Box3)));
   BG_CU(cudaMalloc(&d_keys, N * 8)); BG_CU(cudaMalloc(&d_keys2, N * 8));
   BG_CU(cudaMalloc(&d_vals, N * 4)); BG_CU(cudaMalloc(&d_vals2, N * 4));
-  BG_CU(cudaMalloc(&d_left, N * 4)); BG_CU(cudaMalloc(&d_right, N * 4)); BG_CU(cudaMalloc(&d_first, N * 4)); BG_CU(cudaMalloc(&d_last, N * 4));
+  BG_CU(cudaMalloc(&d_left, N * 4)); BG_CU(cudaMalloc(&d_right, N * 4)); BG_CU(cudaMalloc(&d_count, N * 4));
   BG_CU(cudaMalloc(&d_parent, (2 * N - 1) * 4)); BG_CU(cudaMalloc(&d_arrived, N * 4)); BG_CU(cudaMalloc(&d_order, N * 4));
   BG_CU(cudaMalloc(&d_nodes, N * sizeof(CwNode))); // a wide node consumes at least one binary inner node: < n of them
   BG_CU(cudaMalloc(&d_items[0], N * sizeof(uint2))); BG_CU(cudaMalloc(&d_items[1], N * sizeof(uint2)));
@@ -277,18 +353,44 @@ bool build_cwbvh_device(const std::vector<Box3>& prim_boxes, int max_leaf, std::
   BG_CU(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, d_keys, d_keys2, d_vals, d_vals2, n, 0, 63));
   BG_CU(cudaMalloc(&d_tmp, tmp_bytes));
   BG_CU(cub::DeviceRadixSort::SortPairs(d_tmp, tmp_bytes, d_keys, d_keys2, d_vals, d_vals2, n, 0, 63));
-  k_radix_tree<<<GB, TB>>>(d_keys2, n, d_left, d_right, d_parent, d_first, d_last);
-  BG_CU(cudaMemset(d_arrived, 0, N * 4));
-  k_refit<<<GB, TB>>>(d_boxes, d_vals2, n, d_left, d_right, d_parent, d_arrived, d_nbox);
-  BG_CU(cudaGetLastError());
-  BG_CU(cudaDeviceSynchronize());
+  int root = 0;
+  if (algorithm == 0) { // LBVH: binary radix tree + bottom-up refit
+    k_radix_tree<<<GB, TB>>>(d_keys2, n, d_left, d_right, d_parent, d_count);
+    BG_CU(cudaMemset(d_arrived, 0, N * 4));
+    k_refit<<<GB, TB>>>(d_boxes, d_vals2, n, d_left, d_right, d_parent, d_arrived, d_nbox);
+    BG_CU(cudaGetLastError());
+    BG_CU(cudaDeviceSynchronize());
+  } else { // PLOC
+    for (int k = 0; k < 2; k++) { BG_CU(cudaMalloc(&d_cid[k], N * 4)); BG_CU(cudaMalloc(&d_cbox[k], N * sizeof(Box3))); }
+    BG_CU(cudaMalloc(&d_nn, N * 4)); BG_CU(cudaMalloc(&d_valid, N * 4)); BG_CU(cudaMalloc(&d_pos, N * 4));
+    size_t scan_bytes = 0;
+    BG_CU(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, d_valid, d_pos, n));
+    if (scan_bytes > tmp_bytes) { cudaFree(d_tmp); d_tmp = nullptr; BG_CU(cudaMalloc(&d_tmp, scan_bytes)); tmp_bytes = scan_bytes; }
+    BG_CU(cudaMemset(d_ctr, 0, sizeof(unsigned int))); // inner-node ids are handed out from 0
+    k_ploc_init<<<GB, TB>>>(d_boxes, d_vals2, n, d_cid[0], d_cbox[0], d_nbox);
+    int m = n, rounds = 0;
+    while (m > 1) {
+      const int gb = (m + TB - 1) / TB;
+      k_ploc_nn<<<gb, TB>>>(d_cbox[0], m, d_nn);
+      k_ploc_merge<<<gb, TB>>>(d_cid[0], d_cbox[0], m, d_nn, d_left, d_right, d_count, d_nbox, d_ctr, n, d_cid[1], d_cbox[1], d_valid);
+      BG_CU(cub::DeviceScan::ExclusiveSum(d_tmp, scan_bytes, d_valid, d_pos, m));
+      k_ploc_compact<<<gb, TB>>>(d_cid[1], d_cbox[1], d_valid, d_pos, m, d_cid[0], d_cbox[0]);
+      int last_pos = 0, last_valid = 0;
+      BG_CU(cudaMemcpy(&last_pos, d_pos + (m - 1), 4, cudaMemcpyDeviceToHost));
+      BG_CU(cudaMemcpy(&last_valid, d_valid + (m - 1), 4, cudaMemcpyDeviceToHost));
+      const int m_new = last_pos + last_valid;
+      if (m_new >= m || ++rounds > 100000) { if (err) *err = "build_cwbvh_device: PLOC made no progress"; cleanup(); return false; }
+      m = m_new;
+    }
+    BG_CU(cudaMemcpy(&root, d_cid[0], 4, cudaMemcpyDeviceToHost));
+  }
   // ---- collapse, one launch per level of the wide tree
   unsigned int ctr0[3] = {1u, 0u, 0u}; // node 0 is the root
   BG_CU(cudaMemcpy(d_ctr, ctr0, sizeof(ctr0), cudaMemcpyHostToDevice));
-  const uint2 root_item = make_uint2(0u, 0u);
+  const uint2 root_item = make_uint2((uint32_t)root, 0u);
   BG_CU(cudaMemcpy(d_items[0], &root_item, sizeof(uint2), cudaMemcpyHostToDevice));
   CollapseArgs A;
-  A.n = n; A.max_leaf = max_leaf; A.left = d_left; A.right = d_right; A.first = d_first; A.last = d_last; A.nbox = d_nbox; A.vals = d_vals2;
+  A.n = n; A.max_leaf = max_leaf; A.left = d_left; A.right = d_right; A.count = d_count; A.nbox = d_nbox; A.vals = d_vals2;
   A.nodes = d_nodes; A.order = d_order; A.node_counter = d_ctr; A.prim_counter = d_ctr + 1; A.out_counter = d_ctr + 2;
   int n_in = 1, cur = 0, levels = 0;
   while (n_in > 0) {
@@ -307,7 +409,7 @@ bool build_cwbvh_device(const std::vector<Box3>& prim_boxes, int max_leaf, std::
   out_nodes.resize(ctr[0]); out_prim_order.resize(N);
   BG_CU(cudaMemcpy(out_nodes.data(), d_nodes, (size_t)ctr[0] * sizeof(CwNode), cudaMemcpyDeviceToHost));
   BG_CU(cudaMemcpy(out_prim_order.data(), d_order, N * 4, cudaMemcpyDeviceToHost));
-  if (root_box) BG_CU(cudaMemcpy(root_box, d_nbox, sizeof(Box3), cudaMemcpyDeviceToHost));
+  if (root_box) BG_CU(cudaMemcpy(root_box, d_nbox + root, sizeof(Box3), cudaMemcpyDeviceToHost));
   cleanup();
   return true;
 }

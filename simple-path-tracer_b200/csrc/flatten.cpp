@@ -180,8 +180,12 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
   if (const char* e = getenv("SPT_BLAS_LEAF")) blas_leaf = std::max(1, std::min(3, atoi(e)));
   // BLAS builder: meshes of >= SPT_DEVICE_BUILD_MIN_TRIS triangles are built on the GPU (LBVH, ~100x faster to build, a few
   // per cent slower to trace), smaller ones with the host SAH builder.  SPT_BVH_BUILD=host|device forces one of them.
-  int bvh_mode = 1;
-  if (const char* e = getenv("SPT_BVH_BUILD")) bvh_mode = !strcmp(e, "host") ? 0 : (!strcmp(e, "device") ? 2 : 1);
+  int bvh_mode = 1, bvh_algo = 1; // GPU builder: PLOC (near-SAH quality); SPT_BVH_BUILD=device_lbvh picks the plain radix tree
+  if (const char* e = getenv("SPT_BVH_BUILD")) {
+    bvh_mode = !strcmp(e, "host") ? 0 : (!strncmp(e, "device", 6) ? 2 : 1);
+    if (!strcmp(e, "device_lbvh")) bvh_algo = 0;
+  }
+  if (const char* e = getenv("SPT_BVH_ALGO")) bvh_algo = !strcmp(e, "lbvh") ? 0 : 1;
   for (int mi = 0; mi < d.n_meshes; mi++) {
     const SptMeshDesc& m = d.meshes[mi];
     if (m.n_tris <= 0 || m.n_verts <= 0 || !m.position || !m.index) return bad("mesh: empty");
@@ -213,7 +217,7 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
     const auto tb0 = std::chrono::steady_clock::now();
     if (on_device && m.n_tris >= 2) {
       std::string berr;
-      if (!build_cwbvh_device(boxes, blas_leaf, blas_nodes[mi], blas_order[mi], &mesh_box[mi], &berr)) return bad(berr.c_str());
+      if (!build_cwbvh_device(boxes, blas_leaf, blas_nodes[mi], blas_order[mi], &mesh_box[mi], &berr, bvh_algo)) return bad(berr.c_str());
       hs.blas_on_device++;
     } else build_cwbvh(boxes, blas_leaf, 0, 0, blas_nodes[mi], blas_order[mi], &mesh_box[mi]);
     hs.seconds_bvh += std::chrono::duration<double>(std::chrono::steady_clock::now() - tb0).count();

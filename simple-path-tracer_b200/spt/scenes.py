@@ -203,3 +203,37 @@ def load(name, **kw):
     """FlatScene for a named config."""
     from . import loader
     return loader.load_scene(CONFIGS[name]["scene"](**kw), BASE_PATH)
+
+
+def _abi():
+    from . import abi
+    return abi
+
+
+def flatten_instances(fs):
+    """every trimesh instance of `fs` baked into one world-space mesh behind a single identity instance"""
+    pos, nrm, uv, tan, bit, idx, base = [], [], [], [], [], [], 0
+    keep = []
+    for inst in fs.instances:
+        if inst["prim_kind"] != _abi().PRIM_TRIMESH:
+            keep.append(inst)
+            continue
+        m = fs.meshes[inst["prim_index"]]
+        x = np.asarray(inst["xform"], np.float32)
+        A, t = x[:9].reshape(3, 3).T, x[9:]
+        nA = np.linalg.inv(A.astype(np.float64)).T.astype(np.float32)
+        pos.append(m["positions"] @ A.T + t)
+        n = m["normals"] @ nA.T
+        nrm.append(n / np.maximum(np.linalg.norm(n, axis=1, keepdims=True), 1e-20))
+        uv.append(m["texcoords"]); tan.append(m["tangents"] @ A.T); bit.append(m["bitangents"] @ A.T)
+        idx.append(m["indices"].reshape(-1) + base)
+        base += len(m["positions"])
+    mesh = dict(positions=np.concatenate(pos).astype(np.float32), normals=np.concatenate(nrm).astype(np.float32),
+                texcoords=np.concatenate(uv).astype(np.float32), tangents=np.concatenate(tan).astype(np.float32),
+                bitangents=np.concatenate(bit).astype(np.float32), indices=np.concatenate(idx).astype(np.uint32).reshape(-1, 3), path="<flattened>")
+    surf = next(i["surface"] for i in fs.instances if i["prim_kind"] == _abi().PRIM_TRIMESH)
+    fs.meshes = [mesh]
+    fs.instances = keep + [dict(prim_kind=_abi().PRIM_TRIMESH, prim_index=0, surface=surf,
+                                xform=[1.0, 0, 0, 0, 1.0, 0, 0, 0, 1.0, 0, 0, 0])]
+    fs.lights = [l for l in fs.lights if l["tag"] != _abi().LIGHT["shape"]]
+    return fs
