@@ -91,10 +91,16 @@ class Scene:
         return abi.RenderDesc(camera, width, height, max_depth, abi.SAMPLER[sampler], spp, div[0], div[1], filter_radius,
                               seed, tile[0], tile[1], rank, world_size, pool_size, flags, spp_range[0], spp_range[1])
 
-    def render(self, width, height, want_rgb8=False, **kw):
-        """spt_render: host buffers out.  Returns (mean image [H,W,3] f32, stats) or (mean, rgb8, stats)."""
+    def render(self, width, height, want_rgb8=False, out=None, **kw):
+        """spt_render: host buffers out.  Returns (mean image [H,W,3] f32, stats) or (mean, rgb8, stats).  `out`: an existing
+        C-contiguous f32 [H,W,3] array to receive the image (e.g. page-locked memory, so the device-to-host copy is one DMA)."""
         rd = self.render_desc(width, height, **kw)
-        img = np.zeros((height, width, 3), np.float32)
+        if out is not None:
+            if out.dtype != np.float32 or out.shape != (height, width, 3) or not out.flags["C_CONTIGUOUS"]:
+                raise ValueError("out must be a C-contiguous float32 array of shape (height, width, 3)")
+            img = out
+        else:
+            img = np.zeros((height, width, 3), np.float32)
         rgb8 = np.zeros((height, width, 3), np.uint8) if want_rgb8 else None
         st = abi.Stats()
         abi.check(self.lib, self.lib.spt_render(self.h, C.byref(rd), img.ctypes.data,
