@@ -47,6 +47,12 @@ struct TravCounters { // only maintained by the COUNT instantiations
 #ifndef SPT_NODE_PER_ROUND
 #define SPT_NODE_PER_ROUND 1
 #endif
+#ifndef SPT_TRI_FRCP
+#define SPT_TRI_FRCP 1
+#endif
+#ifndef SPT_INST_UNIFORM_SETUP
+#define SPT_INST_UNIFORM_SETUP 1 // 1: the object-space ray setup of an instance visit runs for small meshes too (no divergent branch)
+#endif
 #ifndef SPT_FETCH_MIN_IDLE
 #define SPT_FETCH_MIN_IDLE 6 // refill the warp once this many lanes are without a ray
 #endif
@@ -69,11 +75,19 @@ SPT_D void ray_setup(RaySetup& r, float3 o, float3 d) {
 
 // float(byte j of x).  I2F.U8 runs on the XU pipe (4 lanes/clk per scheduler: ncu showed XU at 50 % of its peak with 48
 // conversions per node step); SPT_BYTE2F_MAGIC=1 builds 2^23 + q with one PRMT and subtracts 2^23 (ALU + FMA pipes, exact).
+// SPT_BYTE2F_BIAS=1 (default) avoids the conversion altogether: one PRMT drops byte j into mantissa bits 8..15 of 1.0f, giving
+// 1 + q * 2^-15 exactly; node_children() folds the 2^15 into the plane scale and the "1 +" into the plane offset, so the
+// slab FFMA absorbs both (48 XU instructions per node step become 48 ALU ones; see node_children for the error bound).
 #ifndef SPT_BYTE2F_MAGIC
 #define SPT_BYTE2F_MAGIC 0
 #endif
+#ifndef SPT_BYTE2F_BIAS
+#define SPT_BYTE2F_BIAS 0
+#endif
 SPT_D float byte_to_float(uint32_t x, int j) { // j is a compile-time constant after unrolling
-#if SPT_BYTE2F_MAGIC
+#if SPT_BYTE2F_BIAS
+  return __uint_as_float(__byte_perm(x, 0x3F800000u, 0x7604u | ((uint32_t)j << 4)));
+#elif SPT_BYTE2F_MAGIC
   return __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7650u | (uint32_t)j)) - 8388608.0f;
 #else
   return (float)((x >> (8 * j)) & 0xff);
@@ -86,11 +100,26 @@ SPT_D void node_children(const float4* __restrict__ nodes, uint32_t node_index, 
   const float4* np = nodes + (size_t)node_index * 5;
   const float4 n0 = ldg4(np), n1 = ldg4(np + 1), n2 = ldg4(np + 2), n3 = ldg4(np + 3), n4 = ldg4(np + 4);
   const uint32_t eim = __float_as_uint(n0.w);
+#if SPT_BYTE2F_BIAS
+  // byte_to_float() yields v = 1 + q * 2^-15, so with A = 2^15 * s / d and B = (lo - o) / d - A the plane distance q * s / d +
+  // (lo - o) / d is v * A + B.  The rounding of B and of the FFMA costs at most ~2^-8 of one quantisation step (|A| * 2^-23)
+  // when the origin is within a few node widths, and the usual relative 2^-24 otherwise; the near planes are pulled in and
+  // the far planes pushed out by |A| * 2^-21 (2^-6 of a step) per axis, which keeps the test conservative.
+  const float sx = __uint_as_float((uint32_t)((int)(int8_t)(eim & 0xff) + 142) << 23);
+  const float sy = __uint_as_float((uint32_t)((int)(int8_t)((eim >> 8) & 0xff) + 142) << 23);
+  const float sz = __uint_as_float((uint32_t)((int)(int8_t)((eim >> 16) & 0xff) + 142) << 23);
+  const float ax = sx * r.idir.x, ay = sy * r.idir.y, az = sz * r.idir.z;
+  const float cx = fmaf(n0.x - r.o.x, r.idir.x, -ax), cy = fmaf(n0.y - r.o.y, r.idir.y, -ay), cz = fmaf(n0.z - r.o.z, r.idir.z, -az);
+  const float bx = fmaf(fabsf(ax), -4.76837158e-7f, cx), by = fmaf(fabsf(ay), -4.76837158e-7f, cy), bz = fmaf(fabsf(az), -4.76837158e-7f, cz);
+  const float fx = fmaf(fabsf(ax), 4.76837158e-7f, cx), fy = fmaf(fabsf(ay), 4.76837158e-7f, cy), fz = fmaf(fabsf(az), 4.76837158e-7f, cz);
+#else
   const float sx = __uint_as_float((uint32_t)((int)(int8_t)(eim & 0xff) + 127) << 23);
   const float sy = __uint_as_float((uint32_t)((int)(int8_t)((eim >> 8) & 0xff) + 127) << 23);
   const float sz = __uint_as_float((uint32_t)((int)(int8_t)((eim >> 16) & 0xff) + 127) << 23);
   const float ax = sx * r.idir.x, ay = sy * r.idir.y, az = sz * r.idir.z;
   const float bx = (n0.x - r.o.x) * r.idir.x, by = (n0.y - r.o.y) * r.idir.y, bz = (n0.z - r.o.z) * r.idir.z;
+  const float fx = bx, fy = by, fz = bz;
+#endif
   // near/far planes per axis according to the ray direction sign
   const bool nx = r.idir.x < 0.f, ny = r.idir.y < 0.f, nz = r.idir.z < 0.f;
   const uint32_t lox[2] = {__float_as_uint(n2.x), __float_as_uint(n2.y)}, loy[2] = {__float_as_uint(n2.z), __float_as_uint(n2.w)};
@@ -111,9 +140,9 @@ SPT_D void node_children(const float4* __restrict__ nodes, uint32_t node_index, 
 #pragma unroll
     for (int j = 0; j < 4; j++) {
       const int sh = 8 * j;
-      const float t0x = fmaf(byte_to_float(nearx, j), ax, bx), t1x = fmaf(byte_to_float(farx, j), ax, bx);
-      const float t0y = fmaf(byte_to_float(neary, j), ay, by), t1y = fmaf(byte_to_float(fary, j), ay, by);
-      const float t0z = fmaf(byte_to_float(nearz, j), az, bz), t1z = fmaf(byte_to_float(farz, j), az, bz);
+      const float t0x = fmaf(byte_to_float(nearx, j), ax, bx), t1x = fmaf(byte_to_float(farx, j), ax, fx);
+      const float t0y = fmaf(byte_to_float(neary, j), ay, by), t1y = fmaf(byte_to_float(fary, j), ay, fy);
+      const float t0z = fmaf(byte_to_float(nearz, j), az, bz), t1z = fmaf(byte_to_float(farz, j), az, fz);
       const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
       const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax)) * 1.000002f; // conservative against rounding (incl. the approximate 1/d)
       if (cmin <= cmax) hitmask |= ((cb4 >> sh) & 0xffu) << ((bit4 >> sh) & 0xffu);
@@ -133,7 +162,11 @@ SPT_D bool tri_test(const float4* __restrict__ tris, uint32_t tri_index, float3 
   const float3 q = xcross3(d, e2);
   float det = xdot3(e1, q);
   if (det != 0.0f) {
+#if SPT_TRI_FRCP
+    det = __frcp_rn(det); // the correctly rounded reciprocal IS the IEEE quotient 1.0 / det (triangle.rs:131), two instructions shorter
+#else
     det = __fdiv_rn(1.0f, det);
+#endif
     const float3 s = xsub3(o, p0);
     v = xmul(xdot3(s, q), det);
     if (v >= 0.0f) {
@@ -292,6 +325,15 @@ SPT_D bool trav_inst(const DScene& sc, Trav& T, const TravStack& st, TravCounter
   T.blas_base = T.sp; T.cur_inst = iid;
 #if SPT_WORLD_STASH
   st.stash(T.r);
+#endif
+#if SPT_INST_UNIFORM_SETUP
+  // small mesh (kind & 2): its triangles become the pending primitive group, no BLAS node step.  The reciprocal direction is
+  // computed for it all the same: three MUFUs cost less than the divergent branch around them.
+  const bool small = (kind & 2) != 0;
+  ray_setup(T.r, o2, d2);
+  T.ng = make_uint2(small ? 0u : (uint32_t)root, small ? 0u : 0x80000000u);
+  T.tg = make_uint2(small ? (uint32_t)root : 0u, small ? (1u << (kind >> 8)) - 1u : 0u);
+  return false;
 #endif
   if (kind & 2) { // small mesh: its triangles become the pending primitive group, no BLAS node step
     T.r.o = o2; T.r.d = d2;

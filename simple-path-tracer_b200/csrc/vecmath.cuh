@@ -25,7 +25,14 @@ SPT_HD float3 operator*(float3 a, float3 b) { return mk3(a.x * b.x, a.y * b.y, a
 SPT_HD float3 operator/(float3 a, float3 b) { return mk3(a.x / b.x, a.y / b.y, a.z / b.z); }
 SPT_HD float3 operator*(float3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
 SPT_HD float3 operator*(float s, float3 a) { return mk3(a.x * s, a.y * s, a.z * s); }
+#ifndef SPT_VEC_RCP
+#define SPT_VEC_RCP 1 // vector / scalar as one reciprocal and three products (the shading math is 2-ulp anyway: -prec-div=false)
+#endif
+#if SPT_VEC_RCP
+SPT_HD float3 operator/(float3 a, float s) { const float r = 1.0f / s; return mk3(a.x * r, a.y * r, a.z * r); }
+#else
 SPT_HD float3 operator/(float3 a, float s) { return mk3(a.x / s, a.y / s, a.z / s); }
+#endif
 SPT_HD float3 operator-(float3 a) { return mk3(-a.x, -a.y, -a.z); }
 SPT_HD float3& operator+=(float3& a, float3 b) { a = a + b; return a; }
 SPT_HD float3& operator*=(float3& a, float3 b) { a = a * b; return a; }
