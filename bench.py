@@ -278,7 +278,7 @@ def main():
                 "stage_seconds": {"extend": s0["seconds_stage"][1], "shade": s0["seconds_stage"][2], "connect": s0["seconds_stage"][3],
                                   "total": s0["seconds_total"]},
                 "l2": l2,
-                "note": "scene working set (%.2f MB) is L2-resident: the HBM figure is the contract's denominator, the binding roof is instruction issue (ncu: issue-active 73 %%, 13/32 active lanes)" % (info["bytes_total"] / 1e6)}
+                "note": "scene working set (%.2f MB) is L2-resident: the HBM figure is the contract's denominator, the binding roof is instruction issue (ncu: issue-active 72 %%, ALU pipe 50 %%, XU 52 %%, 14/32 active lanes)" % (info["bytes_total"] / 1e6)}
     out = {
         "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": W,
         "ms_per_step": 1e3 * elapsed / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
