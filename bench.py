@@ -250,8 +250,9 @@ def main():
     traffic = None
     try:  # dram__bytes_read.sum + dram__bytes_write.sum of one k_extend launch from the committed ncu --set full capture
         with open(os.path.join(ROOT, "profiles", "r01_ncu_extend_traffic.json")) as fh:
-            traffic = json.load(fh).get("dram_bytes_per_launch")
-    except OSError:
+            cap = json.load(fh)  # captured at a 2^22-slot pool: DRAM bytes per ray of that launch x the rays per launch of this run
+            traffic = cap["dram_bytes_per_launch"] / cap["rays_in_captured_launch"] * rays_per_launch
+    except (OSError, KeyError):
         pass
     # regime (i) of SURVEY §8d: the scene is L2-resident, so the node / triangle / instance fetches are bounded by the
     # L2 -> SM read bandwidth, measured here with a 16-byte-load microbenchmark over a 32 MB read-only set
@@ -269,7 +270,7 @@ def main():
                   "what": "algorithmic node + triangle + instance bytes per ray x rays/s of k_extend (requests that hit L1 never reach L2)"}
     except OSError:
         pass
-    pool_slots = args.pool or min(1 << 22, max(1 << 16, w * h * spp))
+    pool_slots = args.pool or min(1 << 24, max(min(1 << 22, max(1 << 16, w * h * spp)), w * h * spp // world // 16))  # the library's default (spt_api.cu)
     roofline = {"bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                 "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
                 "bytes_per_ray": b_ray, "nodes_per_ray": n_node, "tris_per_ray": n_tri, "insts_per_ray": n_inst,

@@ -304,9 +304,14 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   cudaStream_t st = s->stream;
   const size_t n_px = (size_t)r->width * r->height;
   // ---- buffers
-  // default pool: 2^22 slots (measured optimum on B200 for 1080p..4K frames), fewer for renders smaller than that
+  // default pool: 1/16 of this rank's camera samples, between 2^22 and 2^24 slots (fewer for renders smaller than 2^22 samples).
+  // Every iteration of the wavefront loop pays ~80 us of kernel tails and launch gaps whatever the pool holds, so long renders
+  // want a big pool (C2..C5 at full length: 2^23 +5 %, 2^24 +7..10 % over 2^22; profiles/README.md), while a render of a few
+  // pool-fills spends its time filling and draining the pool and wants a small one (2^22 is the measured optimum below ~64 M
+  // samples, and for scenes so trivial that the loop only streams the pool through HBM, like C1).  2^24 slots = 2.95 GB.
   const unsigned long long all_samples = (unsigned long long)n_px * (unsigned long long)spp_pass;
-  int pool_n = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 22, std::max<unsigned long long>(1ull << 16, all_samples));
+  const unsigned long long pool_lo = std::min<unsigned long long>(1ull << 22, std::max<unsigned long long>(1ull << 16, all_samples));
+  int pool_n = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 24, std::max<unsigned long long>(pool_lo, all_samples / (unsigned long long)world / 16ull));
   pool_n = std::max(SPT_TRAV_BLOCK, (pool_n + SPT_TRAV_BLOCK - 1) / SPT_TRAV_BLOCK * SPT_TRAV_BLOCK);
   const size_t per_slot = sizeof(PathRec) + sizeof(float4) + 3 * sizeof(float4) + sizeof(int32_t) + sizeof(uint32_t) + SPT_NQ * sizeof(uint32_t);
   if (s->pool_n != pool_n) {
