@@ -316,7 +316,13 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   const size_t per_slot = sizeof(PathRec) + sizeof(float4) + 3 * sizeof(float4) + sizeof(int32_t) + sizeof(uint32_t) + SPT_NQ * sizeof(uint32_t);
   if (s->pool_n != pool_n) {
     cudaFree(s->pool_mem); s->pool_mem = nullptr; s->pool_n = 0;
-    CU(cudaMalloc(&s->pool_mem, per_slot * (size_t)pool_n));
+    // a pool the CALLER asked for must fit; the default one shrinks (down to the 2^22 rule) if the device is short of memory
+    while (r->pool_size <= 0 && cudaMalloc(&s->pool_mem, per_slot * (size_t)pool_n) != cudaSuccess) {
+      cudaGetLastError(); s->pool_mem = nullptr;
+      if ((unsigned long long)pool_n / 2 < pool_lo) break;
+      pool_n = std::max(SPT_TRAV_BLOCK, (pool_n / 2 + SPT_TRAV_BLOCK - 1) / SPT_TRAV_BLOCK * SPT_TRAV_BLOCK);
+    }
+    if (!s->pool_mem) CU(cudaMalloc(&s->pool_mem, per_slot * (size_t)pool_n));
     s->pool_n = pool_n; s->pool_bytes = per_slot * (size_t)pool_n;
   }
   if (s->film_px < n_px) { cudaFree(s->film); s->film = nullptr; s->film_spp = 0; CU(cudaMalloc(&s->film, n_px * 3 * sizeof(long long))); s->film_px = n_px; }
