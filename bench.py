@@ -270,7 +270,11 @@ def main():
                   "what": "algorithmic node + triangle + instance bytes per ray x rays/s of k_extend (requests that hit L1 never reach L2)"}
     except OSError:
         pass
-    pool_slots = args.pool or min(1 << 24, max(min(1 << 22, max(1 << 16, w * h * spp)), w * h * spp // world // 16))  # the library's default (spt_api.cu)
+    # the library's default (spt_api.cu): samples/16 per rank within [2^22, 2^24] at first, widened after three iterations to
+    # what finishes the render in ~20 iterations, at most samples/8 (allocated)
+    pool_lo = min(1 << 22, max(1 << 16, w * h * spp))
+    pool_slots = args.pool or min(1 << 24, max(pool_lo, w * h * spp // world // 16))
+    pool_alloc = args.pool or min(1 << 24, max(pool_lo, w * h * spp // world // 8))
     roofline = {"bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                 "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
                 "bytes_per_ray": b_ray, "nodes_per_ray": n_node, "tris_per_ray": n_tri, "insts_per_ray": n_inst,
@@ -286,8 +290,8 @@ def main():
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {w}x{h} @ {spp} spp, max_depth 8, recurrence sampler, box r=0.5",
                    "scene": "bunny_5k x3 (conductor, pbr_metallic iso+aniso) + room + emissive quad, power_is MIS" if args.workload == "c2" else args.workload,
-                   "parallelism": f"tiles{world}", "pool_slots": pool_slots,
-                   "l2_policy": "per-step working set (path pool %d MB + film %d MB) exceeds the 126 MB L2; no explicit flush" % (pool_slots * 176 >> 20, w * h * 24 >> 20)},
+                   "parallelism": f"tiles{world}", "pool_slots": pool_slots, "pool_slots_allocated": pool_alloc,
+                   "l2_policy": "per-step working set (path pool %d MB + film %d MB) exceeds the 126 MB L2; no explicit flush" % (pool_alloc * 176 >> 20, w * h * 24 >> 20)},
         "mrays_per_s": mrays, "rays_per_path": (ext + shadow + probe) / paths,
         "shadow_rays_culled_per_path": sum(s["shadow_culled"] for s in stats) / max(1.0, sum(s["paths"] for s in stats)),
         "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(w * h * 3 * 4)},

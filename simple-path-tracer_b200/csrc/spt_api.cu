@@ -304,15 +304,21 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   cudaStream_t st = s->stream;
   const size_t n_px = (size_t)r->width * r->height;
   // ---- buffers
-  // default pool: 1/16 of this rank's camera samples, between 2^22 and 2^24 slots (fewer for renders smaller than 2^22 samples).
-  // Every iteration of the wavefront loop pays ~80 us of kernel tails and launch gaps whatever the pool holds, so long renders
+  // default pool: sized to this rank's camera samples, between 2^22 and 2^24 slots (fewer for renders smaller than 2^22 samples).
+  // Every iteration of the wavefront loop pays ~110 us of kernel tails and launch gaps whatever the pool holds, so long renders
   // want a big pool (C2..C5 at full length: 2^23 +5 %, 2^24 +7..10 % over 2^22; profiles/README.md), while a render of a few
-  // pool-fills spends its time filling and draining the pool and wants a small one (2^22 is the measured optimum below ~64 M
-  // samples, and for scenes so trivial that the loop only streams the pool through HBM, like C1).  2^24 slots = 2.95 GB.
+  // pool-fills spends its time filling and draining the pool and wants a small one: the measured optimum is a pool that
+  // finishes the render in ~20 iterations.  How many samples an iteration starts depends on how long the scene's paths
+  // live, which the first iterations tell: the render starts on samples/16 slots (right for C1, whose paths mostly end at
+  // their first hit) and, after three iterations, widens the ACTIVE part of the pool up to the allocated samples/8.
+  // 2^24 slots = 2.95 GB.
   const unsigned long long all_samples = (unsigned long long)n_px * (unsigned long long)spp_pass;
   const unsigned long long pool_lo = std::min<unsigned long long>(1ull << 22, std::max<unsigned long long>(1ull << 16, all_samples));
-  int pool_n = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 24, std::max<unsigned long long>(pool_lo, all_samples / (unsigned long long)world / 16ull));
-  pool_n = std::max(SPT_TRAV_BLOCK, (pool_n + SPT_TRAV_BLOCK - 1) / SPT_TRAV_BLOCK * SPT_TRAV_BLOCK);
+  const unsigned long long rank_samples = all_samples / (unsigned long long)world;
+  auto round_pool = [](unsigned long long n) { return (int)std::max<unsigned long long>(SPT_TRAV_BLOCK, (n + SPT_TRAV_BLOCK - 1) / SPT_TRAV_BLOCK * SPT_TRAV_BLOCK); };
+  int pool_n = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 24, std::max<unsigned long long>(pool_lo, rank_samples / 8ull)); // allocated
+  int pool_start = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 24, std::max<unsigned long long>(pool_lo, rank_samples / 16ull)); // active at first
+  pool_n = round_pool(pool_n); pool_start = std::min(pool_n, round_pool(pool_start));
   const size_t per_slot = sizeof(PathRec) + sizeof(float4) + 3 * sizeof(float4) + sizeof(int32_t) + sizeof(uint32_t) + SPT_NQ * sizeof(uint32_t);
   if (s->pool_n != pool_n) {
     cudaFree(s->pool_mem); s->pool_mem = nullptr; s->pool_n = 0;
@@ -320,7 +326,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
     while (r->pool_size <= 0 && cudaMalloc(&s->pool_mem, per_slot * (size_t)pool_n) != cudaSuccess) {
       cudaGetLastError(); s->pool_mem = nullptr;
       if ((unsigned long long)pool_n / 2 < pool_lo) break;
-      pool_n = std::max(SPT_TRAV_BLOCK, (pool_n / 2 + SPT_TRAV_BLOCK - 1) / SPT_TRAV_BLOCK * SPT_TRAV_BLOCK);
+      pool_n = round_pool(pool_n / 2); pool_start = std::min(pool_start, pool_n);
     }
     if (!s->pool_mem) CU(cudaMalloc(&s->pool_mem, per_slot * (size_t)pool_n));
     s->pool_n = pool_n; s->pool_bytes = per_slot * (size_t)pool_n;
@@ -337,7 +343,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
     P.pool.hit_inst = (int32_t*)p; p += N * sizeof(int32_t);
     P.pool.flags = (uint32_t*)p; p += N * sizeof(uint32_t);
     P.queue = (uint32_t*)p; p += N * SPT_NQ * sizeof(uint32_t);
-    P.pool.n = pool_n;
+    P.pool.n = pool_start; // active slots; the arrays hold pool_n
   }
   P.ctr = s->ctr; P.film = s->film;
   // ---- tile ownership: tiles sorted by a hash, dealt round-robin -> interleaved, balanced to +-1 tile
@@ -371,10 +377,15 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
     s->occ_bat = std::max(1, s->occ_bat);
     s->occ_ext = std::max(1, s->occ_ext); s->occ_con = std::max(1, s->occ_con);
   }
-  const int grid_ext = persistent_grid(s->ctx, pool_n, s->occ_ext), grid_con = persistent_grid(s->ctx, pool_n, s->occ_con);
-  const int grid_shade = grid_for(s->ctx, pool_n, 16);
-  const int grid_logic = (pool_n + SPT_LOGIC_BLOCK - 1) / SPT_LOGIC_BLOCK;
-  const int grid_gen = std::min(grid_logic, s->ctx->sm_count * 8);
+  int grid_ext = 0, grid_con = 0, grid_shade = 0, grid_logic = 0, grid_gen = 0;
+  auto set_active_pool = [&](int n) { // between iterations only: the queues are empty then, and slots never used are free slots
+    P.pool.n = n;
+    grid_ext = persistent_grid(s->ctx, n, s->occ_ext); grid_con = persistent_grid(s->ctx, n, s->occ_con);
+    grid_shade = grid_for(s->ctx, n, 16);
+    grid_logic = (n + SPT_LOGIC_BLOCK - 1) / SPT_LOGIC_BLOCK;
+    grid_gen = std::min(grid_logic, s->ctx->sm_count * 8);
+  };
+  set_active_pool(pool_start);
   uint64_t iters = 0, launches = 0;
   const bool timed = (r->flags & SPT_RENDER_TIME_STAGES) != 0;
   double stage[6] = {0, 0, 0, 0, 0, 0}; // generate (inside shade), extend, shade (logic..generate), connect, resolve, other
@@ -420,11 +431,13 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
     // The host only needs the device counters to know when to stop.  While camera samples remain, it looks every
     // `stride` iterations (the cursor tells how far the render is); once the cursor is exhausted the pool drains
     // within max_depth iterations and the host looks after every one.
-    const uint64_t est_total = std::max<uint64_t>(1, P.total_samples / (uint64_t)pool_n);
     bool drain_seen = false;
+    unsigned long long cursor_1 = 0; // cursor after the first iteration (= the pool filled once)
+    bool widen = !timed && pool_n > pool_start;
     for (;;) {
       int stride = 1;
-      if (!timed && iters > 0 && s->h_ctr->cursor < P.total_samples) {
+      if (widen && iters == 1) { cursor_1 = s->h_ctr->cursor; stride = 2; }
+      else if (!timed && iters > 0 && s->h_ctr->cursor < P.total_samples) {
         const double done = (double)s->h_ctr->cursor / (double)P.total_samples;
         const double per_iter = done / (double)iters;                       // fraction of the samples started per iteration
         const double left = per_iter > 0 ? (1.0 - done) / per_iter : 1.0;   // iterations until the cursor runs out
@@ -436,7 +449,14 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
         drain_seen = true;
         stride = std::max(1, r->max_depth - 2);
       }
-      (void)est_total;
+      if (widen && iters == 3) { // samples started per iteration and slot, now that the pool has turned over twice
+        widen = false;
+        const double per_slot_iter = (double)(s->h_ctr->cursor - cursor_1) / (2.0 * (double)P.pool.n);
+        if (per_slot_iter > 0 && s->h_ctr->cursor < P.total_samples) {
+          const double want = (double)P.total_samples / (20.0 * per_slot_iter);
+          set_active_pool(std::min(pool_n, std::max(P.pool.n, round_pool((unsigned long long)want))));
+        }
+      }
       for (int k = 0; k < stride; k++) {
         if (timed) cudaEventRecord(s->sev[0], st);
         iteration();
