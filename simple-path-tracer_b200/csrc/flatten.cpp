@@ -8,6 +8,9 @@
 #include <cstring>
 #include <cfloat>
 #include <chrono>
+#include <thread>
+#include <atomic>
+#include <functional>
 #include <string>
 #include <cstdlib>
 #include <algorithm>
@@ -88,6 +91,20 @@ void tex_average(const HostScene& hs, int id, float out[3]) {
 }
 
 } // namespace
+
+// fn(begin, end) over [0, n) on several host threads: the per-vertex / per-triangle gathers of a big mesh are plain copies
+// into disjoint ranges (10 M triangles: 2.4 GB written), so the result does not depend on the split.
+static void parallel_ranges(size_t n, const std::function<void(size_t, size_t)>& fn) {
+  const size_t min_per_thread = (size_t)1 << 16;
+  size_t nt = std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), 32);
+  nt = std::min(nt, n / min_per_thread);
+  if (nt <= 1) { fn(0, n); return; }
+  std::vector<std::thread> th;
+  const size_t per = (n + nt - 1) / nt;
+  for (size_t t = 0; t < nt; t++) { const size_t b = t * per, e = std::min(n, b + per); if (b < e) th.emplace_back(fn, b, e); }
+  for (auto& x : th) x.join();
+}
+
 
 std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
   auto bad = [](const char* m) { return std::string(m); };
@@ -190,26 +207,42 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
     const SptMeshDesc& m = d.meshes[mi];
     if (m.n_tris <= 0 || m.n_verts <= 0 || !m.position || !m.index) return bad("mesh: empty");
     DMesh dm; dm.vert_base = (int32_t)(hs.verts.size() / 4); dm.idx_base = (int32_t)(hs.indices.size() / 3); dm.n_tris = m.n_tris; dm.blas_root = 0;
-    for (int v = 0; v < m.n_verts; v++) {
-      const float* p = m.position + 3 * v;
-      const float nz[3] = {0, 0, 1}, tx[3] = {1, 0, 0}, by[3] = {0, 1, 0}, uv0[2] = {0, 0};
-      const float* n = m.normal ? m.normal + 3 * v : nz; const float* uv = m.texcoord ? m.texcoord + 2 * v : uv0;
-      const float* t = m.tangent ? m.tangent + 3 * v : tx; const float* b = m.bitangent ? m.bitangent + 3 * v : by;
-      hs.verts.push_back(make_float4(p[0], p[1], p[2], uv[0]));
-      hs.verts.push_back(make_float4(n[0], n[1], n[2], uv[1]));
-      hs.verts.push_back(make_float4(t[0], t[1], t[2], 0.f));
-      hs.verts.push_back(make_float4(b[0], b[1], b[2], 0.f));
+    {
+      const size_t v0 = hs.verts.size();
+      hs.verts.resize(v0 + 4 * (size_t)m.n_verts);
+      float4* out = hs.verts.data() + v0;
+      parallel_ranges((size_t)m.n_verts, [&](size_t vb, size_t ve) {
+        const float nz[3] = {0, 0, 1}, tx[3] = {1, 0, 0}, by[3] = {0, 1, 0}, uv0[2] = {0, 0};
+        for (size_t v = vb; v < ve; v++) {
+          const float* p = m.position + 3 * v;
+          const float* n = m.normal ? m.normal + 3 * v : nz; const float* uv = m.texcoord ? m.texcoord + 2 * v : uv0;
+          const float* t = m.tangent ? m.tangent + 3 * v : tx; const float* b = m.bitangent ? m.bitangent + 3 * v : by;
+          out[4 * v + 0] = make_float4(p[0], p[1], p[2], uv[0]);
+          out[4 * v + 1] = make_float4(n[0], n[1], n[2], uv[1]);
+          out[4 * v + 2] = make_float4(t[0], t[1], t[2], 0.f);
+          out[4 * v + 3] = make_float4(b[0], b[1], b[2], 0.f);
+        }
+      });
     }
     std::vector<Box3> boxes(m.n_tris);
-    for (int t = 0; t < m.n_tris; t++) {
-      Box3 bx; for (int k = 0; k < 3; k++) { bx.lo[k] = FLT_MAX; bx.hi[k] = -FLT_MAX; }
-      for (int c = 0; c < 3; c++) {
-        const uint32_t vi = m.index[3 * t + c];
-        if (vi >= (uint32_t)m.n_verts) return bad("mesh: vertex index out of range");
-        hs.indices.push_back(vi);
-        for (int k = 0; k < 3; k++) { bx.lo[k] = std::min(bx.lo[k], m.position[3 * vi + k]); bx.hi[k] = std::max(bx.hi[k], m.position[3 * vi + k]); }
-      }
-      boxes[t] = bx;
+    {
+      const size_t i0 = hs.indices.size();
+      hs.indices.resize(i0 + 3 * (size_t)m.n_tris);
+      uint32_t* out = hs.indices.data() + i0;
+      std::atomic<bool> bad_index(false);
+      parallel_ranges((size_t)m.n_tris, [&](size_t tb, size_t te) {
+        for (size_t t = tb; t < te; t++) {
+          Box3 bx; for (int k = 0; k < 3; k++) { bx.lo[k] = FLT_MAX; bx.hi[k] = -FLT_MAX; }
+          for (int c = 0; c < 3; c++) {
+            const uint32_t vi = m.index[3 * t + c];
+            if (vi >= (uint32_t)m.n_verts) { bad_index = true; return; }
+            out[3 * t + c] = vi;
+            for (int k = 0; k < 3; k++) { bx.lo[k] = std::min(bx.lo[k], m.position[3 * vi + k]); bx.hi[k] = std::max(bx.hi[k], m.position[3 * vi + k]); }
+          }
+          boxes[t] = bx;
+        }
+      });
+      if (bad_index) return bad("mesh: vertex index out of range");
     }
     hs.meshes[mi] = dm;
     // node/prim bases are patched below once the TLAS size is known: build with base 0 and offset afterwards
@@ -272,29 +305,36 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
     for (CwNode n : blas_nodes[mi]) { n.child_base += node_base; n.prim_base += tri_base; hs.nodes.push_back(n); }
     const SptMeshDesc& m = d.meshes[mi];
     mesh_tri_base[mi] = tri_base;
-    const float nz[3] = {0, 0, 1}, tx[3] = {1, 0, 0}, by[3] = {0, 1, 0}, uv0[2] = {0, 0};
-    for (int t : blas_order[mi]) {
-      float idf; int32_t id = t; memcpy(&idf, &id, 4);
-      const float* P[3]; const float* N[3]; const float* T[3]; const float* B[3]; const float* UV[3];
-      for (int c = 0; c < 3; c++) {
-        const uint32_t vi = m.index[3 * t + c];
-        P[c] = m.position + 3 * vi;
-        N[c] = m.normal ? m.normal + 3 * vi : nz; UV[c] = m.texcoord ? m.texcoord + 2 * vi : uv0;
-        T[c] = m.tangent ? m.tangent + 3 * vi : tx; B[c] = m.bitangent ? m.bitangent + 3 * vi : by;
+    const std::vector<int>& order = blas_order[mi];
+    const size_t t0 = hs.tris.size(), s0 = hs.shade_tris.size();
+    hs.tris.resize(t0 + 3 * order.size()); hs.shade_tris.resize(s0 + 9 * order.size());
+    float4* out_t = hs.tris.data() + t0; float4* out_s = hs.shade_tris.data() + s0;
+    parallel_ranges(order.size(), [&](size_t jb, size_t je) {
+      const float nz[3] = {0, 0, 1}, tx[3] = {1, 0, 0}, by[3] = {0, 1, 0}, uv0[2] = {0, 0};
+      for (size_t j = jb; j < je; j++) {
+        const int t = order[j];
+        float idf; int32_t id = t; memcpy(&idf, &id, 4);
+        const float* P[3]; const float* N[3]; const float* T[3]; const float* B[3]; const float* UV[3];
+        for (int c = 0; c < 3; c++) {
+          const uint32_t vi = m.index[3 * t + c];
+          P[c] = m.position + 3 * vi;
+          N[c] = m.normal ? m.normal + 3 * vi : nz; UV[c] = m.texcoord ? m.texcoord + 2 * vi : uv0;
+          T[c] = m.tangent ? m.tangent + 3 * vi : tx; B[c] = m.bitangent ? m.bitangent + 3 * vi : by;
+        }
+        // (p0, id), e1 = p1 - p0, e2 = p2 - p0: the two edge vectors Triangle::intersect_ray recomputes per test (triangle.rs:128-129)
+        // are stored instead of the vertices — same IEEE subtraction, done once here (this file is built with -ffp-contract=off)
+        out_t[3 * j] = make_float4(P[0][0], P[0][1], P[0][2], idf);
+        for (int c = 1; c < 3; c++) out_t[3 * j + c] = make_float4(P[c][0] - P[0][0], P[c][1] - P[0][1], P[c][2] - P[0][2], 0.f);
+        // Triangle::pdf / BvhAccel::pdf: 1 / max(area, 1e-3) / n_tris (triangle.rs:272-280, bvh.rs:300-302, Q6)
+        const V3 e1{P[1][0] - P[0][0], P[1][1] - P[0][1], P[1][2] - P[0][2]}, e2{P[2][0] - P[0][0], P[2][1] - P[0][1], P[2][2] - P[0][2]};
+        const float area = length(cross(e1, e2)) * 0.5f;
+        const float prim_pdf = (1.0f / std::max(area, 0.001f)) / (float)m.n_tris;
+        const float w[9] = {UV[0][0], UV[0][1], UV[1][0], UV[1][1], UV[2][0], UV[2][1], prim_pdf, 0.f, 0.f};
+        for (int c = 0; c < 3; c++) out_s[9 * j + c] = make_float4(N[c][0], N[c][1], N[c][2], w[c]);
+        for (int c = 0; c < 3; c++) out_s[9 * j + 3 + c] = make_float4(T[c][0], T[c][1], T[c][2], w[3 + c]);
+        for (int c = 0; c < 3; c++) out_s[9 * j + 6 + c] = make_float4(B[c][0], B[c][1], B[c][2], w[6 + c]);
       }
-      // (p0, id), e1 = p1 - p0, e2 = p2 - p0: the two edge vectors Triangle::intersect_ray recomputes per test (triangle.rs:128-129)
-      // are stored instead of the vertices — same IEEE subtraction, done once here (this file is built with -ffp-contract=off)
-      hs.tris.push_back(make_float4(P[0][0], P[0][1], P[0][2], idf));
-      for (int c = 1; c < 3; c++) hs.tris.push_back(make_float4(P[c][0] - P[0][0], P[c][1] - P[0][1], P[c][2] - P[0][2], 0.f));
-      // Triangle::pdf / BvhAccel::pdf: 1 / max(area, 1e-3) / n_tris (triangle.rs:272-280, bvh.rs:300-302, Q6)
-      const V3 e1{P[1][0] - P[0][0], P[1][1] - P[0][1], P[1][2] - P[0][2]}, e2{P[2][0] - P[0][0], P[2][1] - P[0][1], P[2][2] - P[0][2]};
-      const float area = length(cross(e1, e2)) * 0.5f;
-      const float prim_pdf = (1.0f / std::max(area, 0.001f)) / (float)m.n_tris;
-      const float w[9] = {UV[0][0], UV[0][1], UV[1][0], UV[1][1], UV[2][0], UV[2][1], prim_pdf, 0.f, 0.f};
-      for (int c = 0; c < 3; c++) hs.shade_tris.push_back(make_float4(N[c][0], N[c][1], N[c][2], w[c]));
-      for (int c = 0; c < 3; c++) hs.shade_tris.push_back(make_float4(T[c][0], T[c][1], T[c][2], w[3 + c]));
-      for (int c = 0; c < 3; c++) hs.shade_tris.push_back(make_float4(B[c][0], B[c][1], B[c][2], w[6 + c]));
-    }
+    });
     hs.blas_nodes += (int64_t)blas_nodes[mi].size();
   }
   hs.inst_mat.assign(std::max(1, d.n_instances), 0);

@@ -57,8 +57,9 @@ int upload(SptScene* s, const std::vector<T>& v, const T** dptr) {
   DevBuf b; b.bytes = std::max<size_t>(sizeof(T), v.size() * sizeof(T));
   CU(cudaMalloc(&b.d, b.bytes));
   CU(cudaMallocHost(&b.h, b.bytes));
-  memset(b.h, 0, b.bytes);
-  if (!v.empty()) memcpy(b.h, v.data(), v.size() * sizeof(T));
+  const size_t used = v.size() * sizeof(T);
+  if (used) memcpy(b.h, v.data(), used);
+  if (used < b.bytes) memset((char*)b.h + used, 0, b.bytes - used);
   CU(cudaMemcpy(b.d, b.h, b.bytes, cudaMemcpyHostToDevice));
   s->bufs.push_back(b);
   *dptr = reinterpret_cast<const T*>(b.d);

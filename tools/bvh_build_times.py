@@ -10,10 +10,11 @@ for p in (os.path.join(ROOT, "simple-path-tracer_b200"), os.path.join(ROOT, "tes
     sys.path.insert(0, p)
 from spt import core, scenes  # noqa: E402
 
-names = sys.argv[1:]
+names = [a for a in sys.argv[1:] if not a.startswith("--")]
+modes = [a[2:] for a in sys.argv[1:] if a.startswith("--")] or ["host", "device_lbvh", "device"]  # e.g. --device: only the GPU PLOC builder
 ctx = core.Context(0)
 for name in names:
-    for mode in ("host", "device_lbvh", "device"):
+    for mode in modes:
         os.environ["SPT_BVH_BUILD"] = mode
         fs = scenes.load("c5" if name == "c5b" else name)
         if name == "c5b":
