@@ -22,6 +22,7 @@ int fail(int code, const std::string& m) { g_err = m; return code; }
 
 struct DevBuf { // one device allocation + the pinned staging copy used by spt_scene_upload
   void* d = nullptr; void* h = nullptr; size_t bytes = 0;
+  const void* src = nullptr; // big arrays are not staged: they are copied straight from the HostScene vector the scene keeps
 };
 
 } // namespace
@@ -53,14 +54,19 @@ struct SptScene {
 namespace {
 
 template <typename T>
-int upload(SptScene* s, const std::vector<T>& v, const T** dptr) {
+int upload(SptScene* s, const std::vector<T>& v, const T** dptr, bool kept = true) { // kept: v lives as long as the scene (a HostScene member)
   DevBuf b; b.bytes = std::max<size_t>(sizeof(T), v.size() * sizeof(T));
   CU(cudaMalloc(&b.d, b.bytes));
-  CU(cudaMallocHost(&b.h, b.bytes));
   const size_t used = v.size() * sizeof(T);
-  if (used) memcpy(b.h, v.data(), used);
-  if (used < b.bytes) memset((char*)b.h + used, 0, b.bytes - used);
-  CU(cudaMemcpy(b.d, b.h, b.bytes, cudaMemcpyHostToDevice));
+  if (kept && used == b.bytes && used >= ((size_t)32 << 20)) { // pinning and filling a second copy of a GB-sized array costs more than it saves
+    b.src = v.data();
+    CU(cudaMemcpy(b.d, b.src, b.bytes, cudaMemcpyHostToDevice));
+  } else {
+    CU(cudaMallocHost(&b.h, b.bytes));
+    if (used) memcpy(b.h, v.data(), used);
+    if (used < b.bytes) memset((char*)b.h + used, 0, b.bytes - used);
+    CU(cudaMemcpy(b.d, b.h, b.bytes, cudaMemcpyHostToDevice));
+  }
   s->bufs.push_back(b);
   *dptr = reinterpret_cast<const T*>(b.d);
   return SPT_OK;
@@ -120,7 +126,7 @@ int32_t spt_scene_create(SptContext* ctx, const SptSceneDesc* desc, SptScene** o
   {
     std::vector<float4> nodes4(h.nodes.size() * 5);
     if (!h.nodes.empty()) memcpy(nodes4.data(), h.nodes.data(), h.nodes.size() * sizeof(spt::CwNode));
-    UP(nodes4, nodes);
+    if ((st = upload(s, nodes4, &d.nodes, false)) != SPT_OK) { spt_scene_destroy(s); return st; }
   }
   UP(h.tris, tris); UP(h.shade_tris, shade_tris); UP(h.inst_mat, inst_mat); UP(h.tlas_inst, tlas_inst); UP(h.inst, inst); UP(h.inst_shade, inst_shade); UP(h.spheres, spheres);
   UP(h.meshes, meshes); UP(h.verts, verts); UP(h.indices, indices); UP(h.surfaces, surfaces); UP(h.materials, materials);
@@ -155,7 +161,7 @@ int32_t spt_scene_upload(SptScene* s, int64_t* bytes_copied) {
   if (!s) return fail(SPT_ERR_INVALID, "spt_scene_upload: null scene");
   CU(cudaSetDevice(s->ctx->device));
   int64_t total = 0;
-  for (const DevBuf& b : s->bufs) { CU(cudaMemcpyAsync(b.d, b.h, b.bytes, cudaMemcpyHostToDevice, s->stream)); total += (int64_t)b.bytes; }
+  for (const DevBuf& b : s->bufs) { CU(cudaMemcpyAsync(b.d, b.h ? b.h : b.src, b.bytes, cudaMemcpyHostToDevice, s->stream)); total += (int64_t)b.bytes; }
   CU(cudaStreamSynchronize(s->stream));
   if (bytes_copied) *bytes_copied = total;
   return SPT_OK;
@@ -175,7 +181,7 @@ int32_t spt_scene_info(const SptScene* s, SptSceneInfo* out) {
 int32_t spt_scene_destroy(SptScene* s) {
   if (!s) return SPT_OK;
   cudaSetDevice(s->ctx->device);
-  for (DevBuf& b : s->bufs) { cudaFree(b.d); cudaFreeHost(b.h); }
+  for (DevBuf& b : s->bufs) { cudaFree(b.d); if (b.h) cudaFreeHost(b.h); }
   cudaFree(s->pool_mem); cudaFree(s->film); cudaFree(s->ctr); cudaFree(s->batch_next); cudaFree(s->tiles);
   cudaFree(s->out_mean); cudaFree(s->out_rgb8); cudaFreeHost(s->h_ctr);
   if (s->ev[0]) cudaEventDestroy(s->ev[0]);
