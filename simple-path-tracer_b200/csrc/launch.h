@@ -9,7 +9,16 @@
 #define SPT_TRAV_BLOCK 128  // threads per block of every traversal / shade kernel
 #define SPT_LOGIC_BLOCK 256
 #ifndef SPT_FETCH_CHUNK
-#define SPT_FETCH_CHUNK 32  // rays a warp reserves at a time
+#define SPT_FETCH_CHUNK 32  // rays a warp reserves at a time with one atomic: caller ray batches
+#endif
+// ... and in the wavefront loop: pool slots in extend, shadow-queue entries in connect.  64 measured +2..3 % over 32 on C2..C4 and
+// +13 % on C1 at the render-sized pools (96 the same, 128 worse on C5); connect alone is 3 % faster at 32, but not the render
+// with its overlapped streams (profiles/README.md)
+#ifndef SPT_EXTEND_CHUNK
+#define SPT_EXTEND_CHUNK 64
+#endif
+#ifndef SPT_CONNECT_CHUNK
+#define SPT_CONNECT_CHUNK 64
 #endif
 
 struct HitIO { float t, u, v; int prim, inst; };

@@ -15,6 +15,7 @@ SPT_D void flush_trav_counters(DevCounters* ctr, const TravCounters& tc) {
 struct ExtendSrc { // every live path of the pool: closest hit (pt.rs:49-50)
   const RenderParams& P;
   uint32_t n_rays;
+  static constexpr uint32_t kChunk = SPT_EXTEND_CHUNK;
   SPT_D uint32_t total() const { return (uint32_t)P.pool.n; }
   SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
     if (!(P.pool.flags[i] & 1u)) return false;
@@ -31,6 +32,7 @@ struct ExtendSrc { // every live path of the pool: closest hit (pt.rs:49-50)
 struct ConnectSrc { // the queued shadow rays: any hit (pt.rs:81, :169); unoccluded contributions go to the film
   const RenderParams& P;
   uint32_t n, nonfinite;
+  static constexpr uint32_t kChunk = SPT_CONNECT_CHUNK;
   SPT_D uint32_t total() const { return n; }
   SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
     const float4 o4 = P.sq.o[i], d4 = P.sq.d[i];
@@ -77,6 +79,7 @@ struct BatchSrc {
   uint32_t n;
   HitIO* __restrict__ hits;       // closest-hit output or null
   uint8_t* __restrict__ occ;      // any-hit output or null
+  static constexpr uint32_t kChunk = SPT_FETCH_CHUNK;
   SPT_D uint32_t total() const { return n; }
   SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
     const float4 a = ldg4(rays + 2 * (size_t)i), b = ldg4(rays + 2 * (size_t)i + 1);
