@@ -2,6 +2,7 @@
 #include <cstdio>
 #include <chrono>
 #include <cstring>
+#include <cstdlib>
 #include <string>
 #include <vector>
 #include <algorithm>
@@ -388,7 +389,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   auto set_active_pool = [&](int n) { // between iterations only: the queues are empty then, and slots never used are free slots
     P.pool.n = n;
     grid_ext = persistent_grid(s->ctx, n, s->occ_ext); grid_con = persistent_grid(s->ctx, n, s->occ_con);
-    grid_shade = grid_for(s->ctx, n, 16);
+    grid_shade = grid_for(s->ctx, n, 4); // = the resident blocks per SM (ShadeCfg::min_blocks): ONE wave of grid-stride blocks.  16 per SM cost 0.7 % (C2) .. 3.5 % (C3), 5 or 6 (a ragged second wave) 5-20 % of the shade stage
     grid_logic = (n + SPT_LOGIC_BLOCK - 1) / SPT_LOGIC_BLOCK;
     grid_gen = std::min(grid_logic, s->ctx->sm_count * 8);
   };
