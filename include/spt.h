@@ -299,8 +299,12 @@ int32_t spt_scene_destroy(SptScene* scene);
 int32_t spt_trace_batch(SptScene* scene, const SptRay* rays, int64_t n, SptHit* out_hits);
 /* ≙ PrimitiveT::intersect_test (ray.t_max is the t_max argument); out[i] = 1 if occluded. */
 int32_t spt_occluded_batch(SptScene* scene, const SptRay* rays, int64_t n, uint8_t* out);
-/* Same, buffers already resident in device memory; stats may be NULL; runs on `stream`
- * (a cudaStream_t passed as void*, NULL = default stream) without synchronising. */
+/* Same, buffers already resident in device memory; stats may be NULL.  `stream` is a cudaStream_t passed as void*: the batch is
+ * enqueued on it and the call returns without synchronising (unless SPT_RENDER_COUNT_TRAVERSAL asks for stats).  stream == NULL
+ * means the scene's own internal (non-blocking) stream, and the call then returns only after the batch has finished.
+ * Concurrency: batches issued on different caller streams may overlap on the device (each launch has its own fetch cursor, up to
+ * 64 launches in flight); calls on ONE scene handle must still come from one host thread at a time, and
+ * SPT_RENDER_COUNT_TRAVERSAL batches (shared counters) must not overlap each other or a render. */
 int32_t spt_trace_batch_device(SptScene* scene, const SptRay* d_rays, int64_t n, SptHit* d_hits,
                                uint32_t flags, SptStats* stats, void* stream);
 int32_t spt_occluded_batch_device(SptScene* scene, const SptRay* d_rays, int64_t n, uint8_t* d_out,

@@ -163,6 +163,7 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
     for (int k = 0; k < 4; k++) o.tex[k] = m.tex[k];
     const bool need[8][4] = {{1, 0, 0, 0}, {0, 0, 0, 0}, {1, 1, 1, 1}, {0, 0, 1, 1}, {1, 0, 1, 1}, {1, 1, 1, 1}, {1, 1, 1, 1}, {1, 1, 1, 1}};
     for (int k = 0; k < 4; k++) if (need[m.tag][k] && !tex_ok(m.tex[k])) return bad("material: bad texture index");
+    if (m.rough_chan < 0 || m.rough_chan > 3 || m.metal_chan < 0 || m.metal_chan > 3) return bad("material: rough_chan / metal_chan must be a texel channel 0..3");
     hs.materials[i] = o;
   }
   hs.mediums.resize(d.n_mediums);
@@ -373,6 +374,10 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
     env_avg_power = sum / (float)props.size(); // environment.rs:39; power = avg_power * 4 pi (:139-141)
   }
   // ---- lights + light sampler ----------------------------------------------------------------------------------------------------
+  if (d.light_sampler != SPT_LS_UNIFORM && d.light_sampler != SPT_LS_POWER_IS) return bad("light_sampler: unknown kind");
+  // pdf_env_light() reads light_prob[env_light_index] (power_is.rs:91-92): the index must name an entry of the light table
+  if (d.env_light_index >= std::max(1, d.n_lights)) return bad("env_light_index out of range");
+  if (d.env_light_index >= 0 && !d.env) return bad("env_light_index without environment");
   hs.light_sampler = d.light_sampler; hs.env_light_index = d.env_light_index;
   hs.inst_light.assign(std::max(1, d.n_instances), -1);
   hs.lights.resize(d.n_lights);

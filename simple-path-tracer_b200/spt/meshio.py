@@ -11,8 +11,8 @@ f32 = np.float32
 def load_obj(path):
     """Returns (positions[n,3], normals[n,3] or None, texcoords[n,2] or None, indices[t,3]) as float32/uint32.
 
-    All `o`/`g` models of the file are merged the way TriMesh::load does, including its index-offset quirk
-    (Q22: offset = number of indices loaded so far, not the number of vertices; triangle.rs:96-102)."""
+    All `o`/`g` models of the file are merged the way TriMesh::load does (triangle.rs:57-108), except for its index-offset
+    quirk Q22 (offset = number of indices loaded so far, triangle.rs:96-102), which is fixed: offset = running vertex count."""
     v, vt, vn = [], [], []
     models = [[]]  # list of face lists; each face = list of (vi, ti, ni)
     with open(path) as fh:
@@ -44,7 +44,7 @@ def load_obj(path):
                 models[-1].append(face)
     pos_all, nrm_all, uv_all, idx_all = [], [], [], []
     have_n = have_t = False
-    n_indices = 0
+    n_vertices = 0
     for faces in models:
         if not faces:
             continue
@@ -69,8 +69,10 @@ def load_obj(path):
         pos_all += mpos
         nrm_all += mnrm
         uv_all += muv
-        idx_all += [[a + n_indices, b + n_indices, c + n_indices] for a, b, c in midx]  # Q22
-        n_indices += 3 * len(midx)
+        # Q22 FIXED: the reference offsets by the number of INDICES loaded so far (triangle.rs:96-102), which panics or wires
+        # triangles to the wrong vertices for any OBJ with more than one object; the evident intent is the running vertex count
+        idx_all += [[a + n_vertices, b + n_vertices, c + n_vertices] for a, b, c in midx]
+        n_vertices += len(mpos)
     return (np.asarray(pos_all, f32).reshape(-1, 3), np.asarray(nrm_all, f32).reshape(-1, 3),
             np.asarray(uv_all, f32).reshape(-1, 2), np.asarray(idx_all, np.uint32).reshape(-1, 3))
 

@@ -182,15 +182,15 @@ def test_cpp_loader_rejects_what_the_python_loader_rejects(host_bin, tmp_path, m
 
 
 def test_cpp_host_external_files_obj_and_png(host_bin, tmp_path):
-    """external JSON sections (json.rs:212-242), an .obj mesh with shared corners + a quad (tobj triangulation, Q22 with two
-    objects), and a PNG image texture written by PIL and decoded by the host's own reader."""
+    """external JSON sections (json.rs:212-242), an .obj mesh with shared corners + a quad (tobj triangulation, two objects:
+    Q22 fixed), and a PNG image texture written by PIL and decoded by the host's own reader."""
     from PIL import Image
     rng = np.random.RandomState(5)
     img = rng.randint(0, 256, (5, 7, 3), dtype=np.uint8)
     Image.fromarray(img).save(tmp_path / "tex.png")
     (tmp_path / "quad.obj").write_text(
         "v -1 0 -1\nv 1 0 -1\nv 1 0 1\nv -1 0 1\nvt 0 0\nvt 1 0\nvt 1 1\nvt 0 1\nvn 0 1 0\n"
-        "o first\nf 1/1/1 2/2/1 3/3/1\n"  # 3 vertices, 3 indices: Q22's offset (index count) happens to equal the vertex count
+        "o first\nf 1/1/1 2/2/1 3/3/1\n"  # 3 vertices, 3 indices
         "o second\nv 0 1 0\nf 1/1/1 2/2/1 3/3/1 4/4/1\nf -1/3/1 2/2/1 3/3/1\n")
     (tmp_path / "mats.json").write_text(json.dumps([{"type": "lambert", "name": "m", "albedo": "t"}]))
     sd = {"cameras": {"type": "perspective", "name": "c", "eye": [0.0, 1.0, 4.0], "forward": [0.0, 0.0, -1.0], "up": [0.0, 1.0, 0.0], "fov": 50.0},
@@ -212,11 +212,18 @@ def test_cpp_host_external_files_obj_and_png(host_bin, tmp_path):
         else:
             assert words_match(got[k], want[k]).all(), k
     assert len(got["mesh0.indices"]) == 4 * 3 * 4  # triangle + quad (2 triangles) + triangle
-    (tmp_path / "quad.obj").write_text("v 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\no a\nf 1 2 3 4\no b\nf 1 2 3\n")  # Q22 overruns
-    with pytest.raises(Exception):
-        loader.load_scene(str(sj))
-    r = run_host(host_bin, ["--scene", str(sj), "--dump-desc", str(out)], check=False)
-    assert r.returncode == 1 and "out of range" in r.stderr
+    # Q22 fixed (index offset = running VERTEX count): a two-object OBJ whose index count differs from its vertex count — the
+    # reference's offset would overrun here — loads, and its triangles are the triangles of the same faces in one object
+    (tmp_path / "quad.obj").write_text("v 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\no a\nf 1 2 3 4\no b\nf 1 2 3\n")
+    two = loader.load_scene(str(sj)).meshes[0]
+    (tmp_path / "quad.obj").write_text("v 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nf 1 2 3 4\nf 1 2 3\n")
+    one = loader.load_scene(str(sj)).meshes[0]
+    assert two["indices"].shape == one["indices"].shape == (3, 3) and len(two["positions"]) == 7 and len(one["positions"]) == 4
+    assert np.array_equal(two["positions"][two["indices"]], one["positions"][one["indices"]])
+    (tmp_path / "quad.obj").write_text("v 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\no a\nf 1 2 3 4\no b\nf 1 2 3\n")
+    run_host(host_bin, ["--scene", str(sj), "--dump-desc", str(out)])
+    got2 = read_dump(out)
+    assert got2["mesh0.indices"] == python_dump(loader.load_scene(str(sj)))["mesh0.indices"]
 
 
 def test_cpp_renderer_config_and_cli_errors(host_bin, tmp_path):

@@ -145,6 +145,21 @@ def test_image_is_independent_of_pool_size_and_rank_split(scene_pair):
     assert not np.array_equal(base, other)
 
 
+def test_render_finishes_every_sample_when_an_iteration_is_all_tile_padding(scene_pair):
+    """Big tiles on an image whose height is not a multiple of the tile: the bottom tiles hold runs of padding ordinals longer than
+    a small pool, so with max_depth 1 (every path ends at its first hit) a whole iteration can start nothing.  The loop must go on
+    until the sample cursor is exhausted (it used to stop at live == 0 and leave black regions)."""
+    fs, sc, _ = scene_pair("c1b")
+    w, h, spp = 200, 100, 3
+    base, st = sc.render(w, h, spp=spp, seed=8, max_depth=1)
+    big, st2 = sc.render(w, h, spp=spp, seed=8, max_depth=1, tile=(64, 64), pool_size=1024)
+    assert st["paths"] == st2["paths"] == w * h * spp
+    assert np.array_equal(base, big)
+    deep, st3 = sc.render(w, h, spp=spp, seed=8, tile=(64, 64), pool_size=1024)
+    ref, _ = sc.render(w, h, spp=spp, seed=8)
+    assert st3["paths"] == w * h * spp and np.array_equal(deep, ref)
+
+
 @pytest.mark.parametrize("name", ["c2", "c4", "c3"])
 def test_image_is_independent_of_kernel_scheduling(scene_pair, name):
     """Multi-stream overlap, stage timing and the counting build only change WHEN a path is advanced, never what it
