@@ -222,6 +222,8 @@ typedef struct SptBxdfResult {
 #define SPT_RENDER_NO_SORT 2u         /* disable material binning of the shade stage (for A/B timing) */
 #define SPT_RENDER_TIME_STAGES 4u     /* fill seconds_stage[] from CUDA events around every kernel launch (implies SERIAL) */
 #define SPT_RENDER_SERIAL 8u          /* issue every kernel on one stream (default: independent kernels of an iteration overlap) */
+#define SPT_RENDER_DEBUG_NORMAL 32u   /* the reference's cargo feature `debug_normal` (pt.rs:113-118): every camera path ends at its first hit and
+                                         writes 0.5 * inter.normal + 0.5 (misses: the environment, or black); the cheapest first-hit parity image */
 #define SPT_RENDER_ACCUMULATE 16u     /* progressive rendering: keep the film of the previous call on this scene (same width x height)
                                          and add this call's samples to it; the outputs are the mean over all samples so far */
 
@@ -237,7 +239,10 @@ typedef struct SptRenderDesc { /* OutputConfig (renderer/mod.rs:9-14) + PathTrac
   int32_t sampler_kind;    /* SPT_SAMPLER_* */
   int32_t spp;             /* random / recurrence */
   int32_t div_x, div_y;    /* jittered (spp = div_x*div_y) */
-  float filter_radius;     /* box filter, filter/boxf.rs; only r <= 0.5 (own-pixel mean, Q14) is supported */
+  float filter_radius;     /* box filter radius in pixels, filter/boxf.rs, in (0, 3.5].  0.5 = own-pixel mean.  Any other radius reproduces
+                              Film::filter_pixel as written (film.rs:68-91, Q14): the UNWEIGHTED colour sum of every sample of the
+                              (2R+1)^2 neighbour pixels, R = ceil(radius - 0.5), divided by the number of those samples that lie inside the
+                              box — brighter than a mean for every radius but 0.5; a pixel with no sample in the box is inf / NaN */
   uint64_t seed;           /* RNG key; the stream of a path depends only on (seed, pixel, sample) */
   int32_t tile_w, tile_h;  /* screen tile size for rank interleaving (0 = SPT_DEFAULT_TILE_W x _H); multiples of 8 / 4 */
   int32_t rank, world_size;/* this process renders the tiles it owns; others stay 0 */

@@ -11,8 +11,9 @@
 // public interface header include/spt.h (scene description structs).
 //
 // Deliberate deviations from the reference (none changes results for the benchmarked settings):
-//  * Film (core/film.rs) is a running per-pixel f32 sum instead of a Vec of every sample; identical
-//    for the box filter with radius <= 0.5 (Q14), which is all spt.h supports.
+//  * Film (core/film.rs) is a running per-pixel f32 sum instead of a Vec of every sample for the box
+//    filter with radius == 0.5 (identical result, Q14); any other radius keeps the reference's
+//    per-sample film (offset + colour per sample) and reconstructs exactly like film.rs:68-91.
 //  * SmallRng::from_entropy (rng.rs:10) -> xoshiro256++ seeded from (seed, thread); HashMap iteration
 //    order (Q9) -> the order of the arrays in SptSceneDesc.
 //  * JitteredSampler (Q16) terminates after div_x*div_y samples (the evident intent).
@@ -186,7 +187,7 @@ inline Ray shadow_ray_from_medium(Vec3 p, Vec3 light_dir, float light_dist, cons
   return sr;
 }
 
-Color trace_ray(const OrcScene& sc, Ray ray, Rng& rng, int max_depth, PathStats& st) { // pt.rs:39-210
+Color trace_ray(const OrcScene& sc, Ray ray, Rng& rng, int max_depth, PathStats& st, bool debug_normal = false) { // pt.rs:39-210
   Color final_color = BLACK, throughput = WHITE;
   int curr_depth = 0;
   const Medium* curr_medium = nullptr;
@@ -241,6 +242,11 @@ Color trace_ray(const OrcScene& sc, Ray ray, Rng& rng, int max_depth, PathStats&
       }
       break;
     } else { // pt.rs:112-193
+      if (debug_normal) { // cfg!(feature = "debug_normal"), pt.rs:113-118
+        Color nc(inter.normal.x, inter.normal.y, inter.normal.z);
+        final_color = nc * 0.5f + Color(0.5f, 0.5f, 0.5f);
+        break;
+      }
       Vec3 po = ray.point_at(inter.t);
       const Surface* surf = inter.surface;
       Bxdf bxdf = surf->material->bxdf_context(sc.textures, inter); // surface.rs:97-103
@@ -344,11 +350,25 @@ inline void keyed_offset(const SptRenderDesc& r, uint64_t pixel, uint32_t k, Rng
 //             bands, n_threads = 2 x cores by default exactly like pt.rs:243-261);
 // rng_mode 1: keyed/paired (stream per (seed,pixel,sample) and closed-form sampler, same numbers as
 //             the CUDA core; rows are handed out dynamically since the result no longer depends on it).
-extern "C" int32_t orc_render(OrcScene* S, const SptRenderDesc* r, int32_t rng_mode, int32_t n_threads,
-                              float* out_rgb_mean, uint8_t* out_rgb8, SptStats* stats) {
+// Options of the checker that are not part of SptRenderDesc (test infrastructure):
+//   debug_normal  : the reference's `debug_normal` cargo feature (pt.rs:113-118)
+//   sample_clamp  : > 0: ALSO accumulate min(sample, clamp) per channel (non-finite samples skipped) into out_clamped_mean —
+//                   a bounded statistic of the same samples for the statistical image tests (the reference's estimator
+//                   divides by max(pdf, 1e-5) and has a heavy tail)
+struct OrcRenderOpts { int32_t debug_normal; float sample_clamp; float* out_clamped_mean; };
+
+extern "C" int32_t orc_render_ex(OrcScene* S, const SptRenderDesc* r, int32_t rng_mode, int32_t n_threads,
+                                 float* out_rgb_mean, uint8_t* out_rgb8, SptStats* stats, const OrcRenderOpts* opts) {
   if (!S || !r || !out_rgb_mean) { g_err = "null argument"; return SPT_ERR_INVALID; }
   if (r->camera_index < 0 || r->camera_index >= (int)S->cameras.size()) { g_err = "bad camera index"; return SPT_ERR_INVALID; }
-  if (r->filter_radius > 0.5f) { g_err = "only box filter radius <= 0.5 supported"; return SPT_ERR_UNSUPPORTED; }
+  const bool dbg_normal = opts && opts->debug_normal;
+  const float s_clamp = opts && opts->out_clamped_mean ? opts->sample_clamp : 0.0f;
+  // Film (core/film.rs): with radius == 0.5 the reconstruction is the own-pixel mean, accumulated on the fly; any other radius
+  // keeps every sample (offset - 0.5, colour) per pixel as film.rs:10-51 does and filters at the end (film.rs:53-91)
+  const bool keep_film = r->filter_radius != 0.5f;
+  struct SampleData { float ox, oy; Color color; };
+  std::vector<std::vector<SampleData>> film;
+  if (keep_film) film.resize((size_t)r->width * r->height);
   const int W = r->width, H = r->height;
   const Camera& cam = S->cameras[r->camera_index];
   const float aspect = (float)W / (float)H;
@@ -365,7 +385,7 @@ extern "C" int32_t orc_render(OrcScene* S, const SptRenderDesc* r, int32_t rng_m
   auto t_begin = std::chrono::steady_clock::now();
 
   auto shade_pixel = [&](int i, int j, PixelSampler& ps, Rng& rng, PathStats& st) {
-    Color sum = BLACK; float weight_sum = 0.0f;
+    Color sum = BLACK, sumc = BLACK; float weight_sum = 0.0f;
     uint64_t pixel = (uint64_t)j * (uint64_t)W + (uint64_t)i;
     ps.start_pixel();
     for (uint32_t k = 0;; k++) {
@@ -378,10 +398,14 @@ extern "C" int32_t orc_render(OrcScene* S, const SptRenderDesc* r, int32_t rng_m
       float x = (((float)i + ox) * width_inv - 0.5f) * aspect;            // pt.rs:269
       float y = ((float)(H - j - 1) + oy) * height_inv - 0.5f;             // pt.rs:270-271
       Ray ray = cam.generate_ray_with_aux_ray(x, y, aspect * width_inv * spp_sqrt_inv, height_inv * spp_sqrt_inv);
-      Color c = trace_ray(*S, ray, rng, r->max_depth, st);
+      Color c = trace_ray(*S, ray, rng, r->max_depth, st, dbg_normal);
       if (!c.is_finite()) st.nonfinite++;
-      sum += c; weight_sum += 1.0f; // film.rs:82-87 with box r<=0.5: weight 1 per own-pixel sample
+      else if (s_clamp > 0.0f) sumc += Color(std::fmin(c.r, s_clamp), std::fmin(c.g, s_clamp), std::fmin(c.b, s_clamp));
+      if (keep_film) film[pixel].push_back(SampleData{ox - 0.5f, oy - 0.5f, c}); // pt.rs:277-279, film.rs:47-51
+      sum += c; weight_sum += 1.0f; // film.rs:82-87 with box r == 0.5: weight 1 per own-pixel sample
     }
+    if (s_clamp > 0.0f) { float* q = opts->out_clamped_mean + 3 * pixel; q[0] = sumc.r / weight_sum; q[1] = sumc.g / weight_sum; q[2] = sumc.b / weight_sum; }
+    if (keep_film) return; // reconstructed after all threads have finished
     Color mean = sum / weight_sum; // film.rs:90
     float* o = out_rgb_mean + 3 * pixel;
     o[0] = mean.r; o[1] = mean.g; o[2] = mean.b;
@@ -410,6 +434,33 @@ extern "C" int32_t orc_render(OrcScene* S, const SptRenderDesc* r, int32_t rng_m
     });
   }
   for (auto& th : threads) th.join();
+  if (keep_film) { // Film::filter_to_image / filter_pixel, film.rs:53-91 with BoxFilter (boxf.rs:10-34)
+    const float radius = r->filter_radius;
+    const int radius_int = (int)std::ceil(radius - 0.5f); // boxf.rs:12
+    for (int y = 0; y < H; y++) for (int x = 0; x < W; x++) {
+      Color color = BLACK; float weight_sum = 0.0f;
+      for (int j = -radius_int; j <= radius_int; j++) {
+        if (y + j < 0 || y + j >= H) continue;
+        for (int i = -radius_int; i <= radius_int; i++) {
+          if (x + i < 0 || x + i >= W) continue;
+          for (const SampleData& sd : film[(size_t)(y + j) * W + (x + i)]) {
+            const float fx = (float)i + sd.ox, fy = (float)j + sd.oy;
+            const float weight = (std::fabs(fx) <= radius && std::fabs(fy) <= radius) ? 1.0f : 0.0f; // boxf.rs:27-33
+            color += sd.color;      // unweighted (Q14), film.rs:85
+            weight_sum += weight;   // film.rs:86
+          }
+        }
+      }
+      Color mean = color / weight_sum; // film.rs:90
+      float* o = out_rgb_mean + 3 * ((size_t)y * W + x);
+      o[0] = mean.r; o[1] = mean.g; o[2] = mean.b;
+      if (out_rgb8) {
+        uint8_t* q = out_rgb8 + 3 * ((size_t)y * W + x);
+        float v[3] = {mean.r, mean.g, mean.b};
+        for (int c2 = 0; c2 < 3; c2++) { float f = clampf(v[c2] * 255.0f, 0.0f, 255.0f); q[c2] = std::isnan(f) ? 0 : (uint8_t)f; }
+      }
+    }
+  }
   double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
   if (stats) {
     memset(stats, 0, sizeof(*stats));
@@ -424,6 +475,11 @@ extern "C" int32_t orc_render(OrcScene* S, const SptRenderDesc* r, int32_t rng_m
     stats->iterations = (uint64_t)n_threads; // reused: number of host threads
   }
   return SPT_OK;
+}
+
+extern "C" int32_t orc_render(OrcScene* S, const SptRenderDesc* r, int32_t rng_mode, int32_t n_threads,
+                              float* out_rgb_mean, uint8_t* out_rgb8, SptStats* stats) {
+  return orc_render_ex(S, r, rng_mode, n_threads, out_rgb_mean, out_rgb8, stats, nullptr);
 }
 
 // ---- seam B2 on ray batches ---------------------------------------------------------------------------

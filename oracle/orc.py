@@ -37,6 +37,7 @@ def lib():
         L.orc_set_fix_q1.argtypes = [C.c_int32]
         L.orc_set_fix_q1.restype = None
         L.orc_render.argtypes = [vp, C.POINTER(abi.RenderDesc), C.c_int32, C.c_int32, vp, vp, C.POINTER(abi.Stats)]
+        L.orc_render_ex.argtypes = [vp, C.POINTER(abi.RenderDesc), C.c_int32, C.c_int32, vp, vp, C.POINTER(abi.Stats), C.POINTER(RenderOpts)]
         L.orc_trace_batch.argtypes = [vp, vp, C.c_int64, vp, C.c_int32, C.POINTER(abi.Stats)]
         L.orc_occluded_batch.argtypes = [vp, vp, C.c_int64, vp, C.c_int32]
         L.orc_bxdf_batch.argtypes = [vp, vp, C.c_int64, vp]
@@ -55,6 +56,10 @@ def _chk(st):
 
 RAY_DT = np.dtype([("origin", "<f4", 3), ("t_min", "<f4"), ("direction", "<f4", 3), ("t_max", "<f4")])
 HIT_DT = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim_id", "<i4"), ("inst_id", "<i4")])
+
+
+class RenderOpts(C.Structure):  # OrcRenderOpts, oracle.cpp
+    _fields_ = [("debug_normal", C.c_int32), ("sample_clamp", C.c_float), ("out_clamped_mean", C.c_void_p)]
 
 
 class OracleScene:
@@ -79,16 +84,23 @@ class OracleScene:
             pass
 
     def render(self, width, height, spp=16, max_depth=8, sampler="recurrence", div=(1, 1), seed=1, camera=0,
-               rng_mode=1, n_threads=0, want_rgb8=False):
-        """rng_mode 0 = reference-faithful per-thread streams, 1 = keyed (paired with the CUDA core)."""
-        rd = abi.RenderDesc(camera, width, height, max_depth, abi.SAMPLER[sampler], spp, div[0], div[1], 0.5, seed,
+               rng_mode=1, n_threads=0, want_rgb8=False, filter_radius=0.5, debug_normal=False, sample_clamp=0.0):
+        """rng_mode 0 = reference-faithful per-thread streams, 1 = keyed (paired with the CUDA core).
+        filter_radius != 0.5 keeps the reference's per-sample film (film.rs); debug_normal = the cargo feature of pt.rs:113-118;
+        sample_clamp > 0 also returns the per-pixel mean of min(sample, clamp) as st["clamped_mean"]."""
+        rd = abi.RenderDesc(camera, width, height, max_depth, abi.SAMPLER[sampler], spp, div[0], div[1], filter_radius, seed,
                             0, 0, 0, 1, 0, 0)
         img = np.zeros((height, width, 3), np.float32)
         rgb8 = np.zeros((height, width, 3), np.uint8) if want_rgb8 else None
+        clamped = np.zeros((height, width, 3), np.float32) if sample_clamp > 0 else None
         st = abi.Stats()
-        _chk(lib().orc_render(self.h, C.byref(rd), rng_mode, n_threads, img.ctypes.data,
-                              rgb8.ctypes.data if want_rgb8 else None, C.byref(st)))
-        return (img, rgb8, st.as_dict()) if want_rgb8 else (img, st.as_dict())
+        opts = RenderOpts(1 if debug_normal else 0, sample_clamp, clamped.ctypes.data if clamped is not None else None)
+        _chk(lib().orc_render_ex(self.h, C.byref(rd), rng_mode, n_threads, img.ctypes.data,
+                                 rgb8.ctypes.data if want_rgb8 else None, C.byref(st), C.byref(opts)))
+        d = st.as_dict()
+        if clamped is not None:
+            d["clamped_mean"] = clamped
+        return (img, rgb8, d) if want_rgb8 else (img, d)
 
     def trace(self, rays, n_threads=0):
         rays = np.ascontiguousarray(rays, RAY_DT)

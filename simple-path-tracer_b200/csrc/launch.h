@@ -35,6 +35,8 @@ void launch_special(const DScene& sc, const RenderParams& P, int grid, cudaStrea
 void launch_shade(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st); // mat = -1: unsorted
 void launch_generate(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st);
 void launch_resolve(const long long* film, int n_pixels, float inv_spp, float* out_mean, uint8_t* out_rgb8, int grid, cudaStream_t st);
+void launch_resolve_box(const RenderParams& P, int k0, int n_k, float radius, int radius_int, float* out_mean, uint8_t* out_rgb8, int grid, cudaStream_t st);
+void launch_aov_normal(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st);
 void launch_bxdf(const DScene& sc, const SptBxdfQuery* q, long long n, SptBxdfResult* out, int grid, cudaStream_t st);
 // defined per shade translation unit
 void launch_shade_a(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st); // 0..3

@@ -171,6 +171,72 @@ __global__ void k_resolve(const long long* __restrict__ film, int n_pixels, floa
 }
 
 
+// ---- resolve for any box radius: Film::filter_pixel (film.rs:68-91) with BoxFilter (boxf.rs:10-34), quirk Q14 ------------------------
+// The reference keeps every sample (offset - 0.5, colour) and reconstructs pixel (x, y) as
+//     sum of the UNWEIGHTED colours of all samples of the (2R+1)^2 neighbour pixels, R = ceil(radius - 0.5)
+//   / number of those samples whose position relative to the pixel centre, (i + ox - 0.5, j + oy - 0.5), lies in the box.
+// The numerator only needs the per-pixel sums the film already holds.  The denominator needs the sub-pixel offset of every sample,
+// which is a closed-form function of (pixel, k) for all three samplers (pixel_offset(): R2 ordinal, or the first draws of the
+// path's keyed stream) — so it is recomputed here instead of being stored: no per-sample memory, (2R+1)^2 * spp offset
+// evaluations per pixel (C2 at radius 1.5: 4.8 G evaluations, a few ms).
+__global__ void k_resolve_box(const RenderParams P, int k0, int n_k, float radius, int radius_int, float* __restrict__ out_mean,
+                              uint8_t* __restrict__ out_rgb8) {
+  const int n_px = P.width * P.height;
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < n_px; p += gridDim.x * blockDim.x) {
+    const int x = p % P.width, y = p / P.width;
+    long long sum[3] = {0, 0, 0};
+    uint32_t in_box = 0;
+    for (int j = -radius_int; j <= radius_int; j++) {
+      if (y + j < 0 || y + j >= P.height) continue;
+      for (int i = -radius_int; i <= radius_int; i++) {
+        if (x + i < 0 || x + i >= P.width) continue;
+        const uint32_t q = (uint32_t)((y + j) * P.width + (x + i));
+        sum[0] += P.film[3 * (size_t)q]; sum[1] += P.film[3 * (size_t)q + 1]; sum[2] += P.film[3 * (size_t)q + 2];
+        for (int k = k0; k < k0 + n_k; k++) {
+          PathRng rng; rng.state = rng_init(P.seed, q, (uint32_t)k);
+          float ox, oy;
+          pixel_offset(P, q, (uint32_t)k, rng, ox, oy);
+          const float fx = (float)i + (ox - 0.5f), fy = (float)j + (oy - 0.5f); // pt.rs:277-279: the film stores offset - 0.5
+          if (fabsf(fx) <= radius && fabsf(fy) <= radius) in_box++;            // BoxFilter::weight, boxf.rs:27-33
+        }
+      }
+    }
+    const float inv = 1.0f / (float)in_box; // Color / f32 multiplies by the reciprocal (color.rs:125-139); 0 samples in the box -> inf / NaN as in the reference
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      const float m = (float)((double)sum[c] * (1.0 / 16777216.0)) * inv;
+      out_mean[3 * (size_t)p + c] = m;
+      if (out_rgb8) out_rgb8[3 * (size_t)p + c] = (uint8_t)clampf_(m * 255.0f, 0.0f, 255.0f);
+    }
+  }
+}
+
+// ---- debug_normal AOV (the reference's cargo feature `debug_normal`, pt.rs:113-118) ---------------------------------------------------
+// Takes the place of logic + special + shade in the wavefront loop: every live path is a camera ray that k_extend has just traced.
+// First surface hit -> colour = 0.5 * inter.normal + 0.5 (the interpolated, instance-transformed normal of Triangle::intersect /
+// Sphere::intersect, not the normal-mapped shading frame); miss -> the environment as at depth 0 (pt.rs:97-111); path ends.
+__global__ void __launch_bounds__(SPT_LOGIC_BLOCK) k_aov_normal(const DScene sc, const RenderParams P) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) { P.ctr->it.live = 0; P.ctr->it.next_ext = 0; P.ctr->it.sq = 0; P.ctr->it.next_con = 0; }
+  uint32_t nonfinite = 0;
+  for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < P.pool.n; slot += gridDim.x * blockDim.x) {
+    const uint32_t flags = P.pool.flags[slot];
+    if (!(flags & 1u)) continue;
+    PathRegs s; HitRec hit;
+    load_path(P, slot, flags, s, hit);
+    if (hit.inst >= 0) {
+      HitGeom g;
+      load_hit(sc, s.ro, s.rd, hit, g);
+      film_add(P, s.pixel, g.n * 0.5f + mk3(0.5f), nonfinite);
+    } else if (sc.env_tex) {
+      float3 env; float env_pdf;
+      env_eval_dir(sc, s.rd, env, env_pdf);
+      film_add(P, s.pixel, env, nonfinite);
+    }
+    P.pool.flags[slot] = 0u;
+  }
+  warp_sum_to(&P.ctr->nonfinite, nonfinite);
+}
+
 // ---- BxDF test hook = BxdfT::{sample,pdf,bxdf,is_delta} with caller-supplied random numbers -----------------------------------
 __global__ void k_bxdf_batch(const DScene sc, const SptBxdfQuery* __restrict__ q, long long n, SptBxdfResult* __restrict__ out) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
@@ -201,6 +267,10 @@ void launch_generate(const DScene& sc, const RenderParams& P, int grid, cudaStre
 void launch_resolve(const long long* film, int n_pixels, float inv_spp, float* out_mean, uint8_t* out_rgb8, int grid, cudaStream_t st) {
   k_resolve<<<grid, 256, 0, st>>>(film, n_pixels, inv_spp, out_mean, out_rgb8);
 }
+void launch_resolve_box(const RenderParams& P, int k0, int n_k, float radius, int radius_int, float* out_mean, uint8_t* out_rgb8, int grid, cudaStream_t st) {
+  k_resolve_box<<<grid, 128, 0, st>>>(P, k0, n_k, radius, radius_int, out_mean, out_rgb8);
+}
+void launch_aov_normal(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st) { k_aov_normal<<<grid, SPT_LOGIC_BLOCK, 0, st>>>(sc, P); }
 void launch_bxdf(const DScene& sc, const SptBxdfQuery* q, long long n, SptBxdfResult* out, int grid, cudaStream_t st) {
   k_bxdf_batch<<<grid, SPT_BLOCK, 0, st>>>(sc, q, n, out);
 }

@@ -7,6 +7,7 @@
 #include <vector>
 #include <algorithm>
 #include <new>
+#include <cmath>
 #include "../../include/spt.h"
 #include "flatten.h"
 #include "launch.h"
@@ -42,6 +43,7 @@ struct SptScene {
   void* pool_mem = nullptr; size_t pool_bytes = 0; int pool_n = 0;
   long long* film = nullptr; size_t film_px = 0; // film_px = allocated pixels
   int film_w = 0, film_h = 0, film_spp = 0;       // what the film currently holds: frame size and samples per pixel accumulated
+  int film_k0 = 0; bool film_contiguous = true;   // ... and which: the samples [film_k0, film_k0 + film_spp) of every pixel, if the passes were consecutive
   DevCounters* ctr = nullptr;
   uint32_t* batch_next = nullptr; uint32_t batch_seq = 0; // ring of SPT_BATCH_CURSORS ray-fetch cursors: one per batch launch in flight
   void* stage_rays = nullptr; void* stage_out = nullptr; size_t stage_rays_bytes = 0, stage_out_bytes = 0; // device staging of the host-buffer entry points (grown on demand, kept)
@@ -316,7 +318,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   if (r->width <= 0 || r->height <= 0 || r->max_depth < 0 || r->max_depth > 255) return fail(SPT_ERR_INVALID, "spt_render: bad width/height/max_depth");
   if (r->camera_index < 0 || r->camera_index >= (int)s->cameras.size()) return fail(SPT_ERR_INVALID, "spt_render: bad camera index");
   if (r->sampler_kind < 0 || r->sampler_kind > 2) return fail(SPT_ERR_INVALID, "spt_render: unknown sampler");
-  if (r->filter_radius > 0.5f) return fail(SPT_ERR_UNSUPPORTED, "spt_render: only the box filter with radius <= 0.5 (own-pixel mean) is supported");
+  if (!(r->filter_radius > 0.0f) || r->filter_radius > 3.5f) return fail(SPT_ERR_INVALID, "spt_render: box filter radius must be in (0, 3.5]");
   if (s->hs.lights.empty()) return fail(SPT_ERR_UNSUPPORTED, "spt_render: the scene has no light (the reference's light sampler would panic)");
   const int world = std::max(1, r->world_size), rank = r->rank;
   if (rank < 0 || rank >= world) return fail(SPT_ERR_INVALID, "spt_render: bad rank");
@@ -395,7 +397,12 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   ds.camera = s->cameras[r->camera_index];
   const bool count = (r->flags & SPT_RENDER_COUNT_TRAVERSAL) != 0;
   // ---- run
-  if (!accumulate) { CU(cudaMemsetAsync(s->film, 0, n_px * 3 * sizeof(long long), st)); s->film_spp = 0; }
+  if (!accumulate) { CU(cudaMemsetAsync(s->film, 0, n_px * 3 * sizeof(long long), st)); s->film_spp = 0; s->film_k0 = spp_first; s->film_contiguous = true; }
+  else if (spp_first != s->film_k0 + s->film_spp) s->film_contiguous = false;
+  // a radius other than 0.5 reconstructs from the sub-pixel offsets of the accumulated samples, recomputed from (pixel, k): the film
+  // must hold one consecutive range of sample indices (rendered with this call's seed and sampler)
+  if (r->filter_radius != 0.5f && !s->film_contiguous)
+    return fail(SPT_ERR_UNSUPPORTED, "spt_render: a box filter radius other than 0.5 needs progressive passes over consecutive sample ranges");
   s->film_w = r->width; s->film_h = r->height; s->film_spp += spp_pass;
   CU(cudaMemsetAsync(s->ctr, 0, sizeof(DevCounters), st));
   CU(cudaMemsetAsync(P.pool.flags, 0, (size_t)pool_n * sizeof(uint32_t), st));
@@ -425,7 +432,15 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   // one persistent kernel is filled by the blocks of the next (serial = one stream, used for per-stage timing).
   const bool serial = timed || (r->flags & SPT_RENDER_SERIAL) != 0;
   bool con_pending = false;
+  const bool aov_normal = (r->flags & SPT_RENDER_DEBUG_NORMAL) != 0;
   auto iteration = [&]() {
+    if (aov_normal) { // pt.rs:113-118: every path ends at its first hit; no shading, no shadow rays
+      spt::launch_aov_normal(ds, P, grid_gen, st);
+      spt::launch_generate(ds, P, grid_gen, st);
+      spt::launch_extend(ds, P, count, grid_ext, st);
+      launches += 3; iters++;
+      return;
+    }
     if (con_pending) { cudaStreamWaitEvent(st, s->ev_con, 0); con_pending = false; } // logic resets the shadow-queue counters
     spt::launch_logic(ds, P, grid_logic, st); launches++;
     if (special) { spt::launch_special(ds, P, grid_shade, st); launches++; }
@@ -456,7 +471,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
     }
     launches += 2; iters++;
   };
-  if (r->max_depth > 0 && P.total_samples > 0) {
+  if ((r->max_depth > 0 || aov_normal) && P.total_samples > 0) {
     // The host only needs the device counters to know when to stop.  While camera samples remain, it looks every
     // `stride` iterations (the cursor tells how far the render is); once the cursor is exhausted the pool drains
     // within max_depth iterations and the host looks after every one.
@@ -505,7 +520,11 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
       if (s->h_ctr->it.live == 0 && s->h_ctr->cursor >= P.total_samples) break;
     }
   }
-  spt::launch_resolve(s->film, (int)n_px, 1.0f / (float)s->film_spp, d_mean, d_rgb8, grid_for(s->ctx, (long long)n_px * 3, 8), st);
+  if (r->filter_radius == 0.5f) // own-pixel mean (Q14: radius_int = 0 and every sample of the pixel lies in the box)
+    spt::launch_resolve(s->film, (int)n_px, 1.0f / (float)s->film_spp, d_mean, d_rgb8, grid_for(s->ctx, (long long)n_px * 3, 8), st);
+  else
+    spt::launch_resolve_box(P, s->film_k0, s->film_spp, r->filter_radius, (int)std::ceil(r->filter_radius - 0.5f), d_mean, d_rgb8,
+                            grid_for(s->ctx, (long long)n_px, 16), st);
   launches++;
   CU(cudaEventRecord(s->ev[1], st));
   CU(cudaMemcpyAsync(s->h_ctr, s->ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, st));
@@ -542,7 +561,7 @@ extern "C" int32_t spt_film_load(SptScene* s, const int64_t* values, int32_t wid
   const size_t n_px = (size_t)width * height;
   if (s->film_px < n_px) { cudaFree(s->film); s->film = nullptr; s->film_spp = 0; CU(cudaMalloc(&s->film, n_px * 3 * sizeof(long long))); s->film_px = n_px; }
   CU(cudaMemcpy(s->film, values, n_px * 3 * sizeof(long long), cudaMemcpyHostToDevice));
-  s->film_w = width; s->film_h = height; s->film_spp = spp_done;
+  s->film_w = width; s->film_h = height; s->film_spp = spp_done; s->film_k0 = 0; s->film_contiguous = true; // a checkpoint holds samples [0, spp_done)
   return SPT_OK;
 }
 

@@ -12,6 +12,7 @@
 //                       the tiles it owns (no gather)
 //   --frames N          render the frame N times (same seed) and report the last one: steady-state timing without the
 //                       first call's allocations and NCCL connection set-up
+//   --debug-normal      first-hit normal AOV = the reference built with `--features debug_normal` (pt.rs:113-118)
 //   --passes N          progressive rendering: the frame's spp in N passes over consecutive sample ranges (SPT_RENDER_ACCUMULATE);
 //                       the image file is rewritten after every pass
 //   --checkpoint FILE   after every pass, write the film (int64 fixed-point sums) + how many samples it holds
@@ -47,6 +48,7 @@ int main(int argc, char** argv) {
   int width = 512, height = 512, device = -1, pool = 0, spp = 0, rank = 0, world = 1, gpus = 0, frames = 1, passes = 1;
   std::string checkpoint, resume;
   std::string nccl_id;
+  bool debug_normal = false;
   uint64_t seed = 1;
   for (int i = 1; i < argc; i++) {
     const std::string a = argv[i];
@@ -71,6 +73,7 @@ int main(int argc, char** argv) {
     else if (a == "--passes") passes = std::max(1, atoi(val().c_str()));
     else if (a == "--checkpoint") checkpoint = val();
     else if (a == "--resume") resume = val();
+    else if (a == "--debug-normal") debug_normal = true; // the reference's cargo feature `debug_normal` (pt.rs:113-118)
     else if (a == "--raw") raw = val();
     else if (a == "--dump-desc") dump = val();
     else { fprintf(stderr, "error: unknown argument '%s'\n", a.c_str()); return 2; }
@@ -115,7 +118,7 @@ int main(int argc, char** argv) {
     if (spp > 0) rc.sampler.spp = spp;
     std::unique_ptr<Renderer> renderer(create_renderer(renderer_type.empty() ? rc.type : renderer_type, rc.max_depth, rc.sampler, rc.filter));
     WavefrontPathTracer* wf = dynamic_cast<WavefrontPathTracer*>(renderer.get());
-    if (wf) { wf->seed = seed; wf->pool_size = pool; wf->rank = rank; wf->world_size = world; }
+    if (wf) { wf->seed = seed; wf->pool_size = pool; wf->rank = rank; wf->world_size = world; if (debug_normal) wf->flags |= SPT_RENDER_DEBUG_NORMAL; }
     DeviceScene scene(fs, device);
     std::unique_ptr<RankGroup> group;
     if (world > 1 && !nccl_id.empty()) { group.reset(new RankGroup(rank, world, device, nccl_id)); if (wf) wf->group = group.get(); }

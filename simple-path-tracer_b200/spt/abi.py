@@ -25,6 +25,7 @@ RENDER_NO_SORT = 2
 RENDER_TIME_STAGES = 4
 RENDER_SERIAL = 8
 RENDER_ACCUMULATE = 16
+RENDER_DEBUG_NORMAL = 32
 
 
 class MeshDesc(C.Structure):

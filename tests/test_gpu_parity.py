@@ -15,7 +15,7 @@ from test_oracle_kat import MATS, material_scene, _queries
 
 pytestmark = pytest.mark.gpu
 G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-SCENES = ["c1", "c1b", "c2", "c3", "c4"]
+SCENES = ["c1", "c1b", "c2", "c3", "c4", "c5"]  # c5 = the north star's multi-GPU config: 2000 instances, deep TLAS
 
 
 def _assert_hits(cmp_):
@@ -40,6 +40,59 @@ def test_ray_batches_match_oracle(scene_pair, name):
     sr = R.incoherent_rays(fs, 1 << 17, seed=77)
     sr["t_max"] = R.FMAX
     assert (osc.occluded(sr) == sc.occluded(sr)).mean() >= 0.9999
+
+
+def _batches_vs_oracle(fs, sc, osc, pw=512, ph=288, n_inc=1 << 19):
+    """P / D / U closest-hit batches + finite and unbounded any-hit batches of one CUDA scene against the oracle"""
+    pr = R.primary_rays(fs, pw, ph)
+    ref, _ = osc.trace(pr)
+    _assert_hits(R.compare_hits(ref, sc.trace(pr)))
+    br = R.bounce_rays(pr, ref)
+    _assert_hits(R.compare_hits(osc.trace(br)[0], sc.trace(br)))
+    ir = R.incoherent_rays(fs, n_inc)
+    c = R.compare_hits(osc.trace(ir)[0], sc.trace(ir))
+    _assert_hits(c)
+    assert c["bit_exact_t"] >= 0.9999
+    fr = R.incoherent_rays(fs, n_inc, finite_tmax=True)
+    assert (osc.occluded(fr) == sc.occluded(fr)).mean() >= 0.9999
+    sb = br.copy(); sb["t_max"] = (np.float32(0.5) + np.arange(len(sb), dtype=np.float32) % np.float32(7.0))  # shadow-ray-like: from surfaces, finite
+    assert (osc.occluded(sb) == sc.occluded(sb)).mean() >= 0.9999
+
+
+@pytest.mark.parametrize("name", ["c2", "c5", "c4"])
+@pytest.mark.parametrize("builder", ["device", "device_lbvh"])
+def test_ray_batches_match_oracle_with_gpu_built_blas(ctx, scene_pair, monkeypatch, name, builder):
+    """The same oracle comparison with every BLAS built by bvh_build_gpu.cu (PLOC / LBVH) instead of the host SAH builder —
+    the builder that is the default for meshes of >= 2^18 triangles, forced here on the benchmark scenes."""
+    from spt import core
+    fs, _, osc = scene_pair(name)
+    monkeypatch.setenv("SPT_BVH_BUILD", builder)
+    sc = core.Scene(ctx, fs)
+    monkeypatch.delenv("SPT_BVH_BUILD")
+    assert sc.info()["blas_on_device"] == len(fs.meshes)
+    _batches_vs_oracle(fs, sc, osc, 384, 216, 1 << 18)
+    gi, gst = sc.render(128, 72, spp=4, seed=11)
+    oi, ost = osc.render(128, 72, spp=4, seed=11, rng_mode=1)
+    rel = np.abs(gi - oi) / (np.abs(oi) + 1e-3)
+    assert float((rel.max(-1) < 1e-3).mean()) >= 0.99 and gst["paths"] == ost["paths"]
+    sc.close()
+
+
+def test_c5b_flattened_mesh_with_default_gpu_built_blas_matches_oracle(ctx):
+    """C5b at 1/16 scale: 120 bunny instances baked into ONE mesh of 600 000 unique triangles (>= 2^18, so flatten() builds its BLAS
+    with the GPU PLOC builder by default), against the oracle's own BVH over the same mesh (BvhAccel::intersect, bvh.rs:262-283)."""
+    import orc
+    from spt import core, scenes
+    fs = scenes.flatten_instances(scenes.load("c5", nx=12, nz=10))
+    assert len(fs.meshes) == 1 and len(fs.meshes[0]["indices"]) == 600000
+    sc, osc = core.Scene(ctx, fs), orc.OracleScene(fs, fix_q1=True)
+    assert sc.info()["blas_on_device"] == 1
+    _batches_vs_oracle(fs, sc, osc, 512, 288, 1 << 18)
+    gi, gst = sc.render(128, 72, spp=4, seed=3)
+    oi, ost = osc.render(128, 72, spp=4, seed=3, rng_mode=1)
+    rel = np.abs(gi - oi) / (np.abs(oi) + 1e-3)
+    assert float((rel.max(-1) < 1e-3).mean()) >= 0.99 and gst["paths"] == ost["paths"]
+    sc.close()
 
 
 @pytest.mark.parametrize("name", SCENES)
@@ -250,11 +303,83 @@ def test_delta_lights_and_spot(ctx):
         sc.close()
 
 
+def _r2_offsets(w, h, spp):
+    """closed-form sub-pixel offsets of the recurrence sampler (csrc/rng.cuh r2_offset): arrays [h*w, spp]"""
+    pix = np.arange(w * h, dtype=np.uint64)[:, None]
+    n = ((pix * np.uint64(spp) + np.arange(spp, dtype=np.uint64)[None, :]) & np.uint64(0xFFFFFFFF)).astype(np.uint32) + np.uint32(1)
+    X = (np.uint32(0x80000000) + n * np.uint32(3242174889)).astype(np.uint32)
+    Y = (np.uint32(0x80000000) + n * np.uint32(2447445413)).astype(np.uint32)
+    return (X >> np.uint32(8)).astype(np.float32) * np.float32(1 / 16777216.0), (Y >> np.uint32(8)).astype(np.float32) * np.float32(1 / 16777216.0)
+
+
+@pytest.mark.parametrize("radius", [1.0, 1.5, 0.3, 2.5])
+def test_box_filter_radius_reproduces_film_rs(scene_pair, radius):
+    """Film::filter_pixel with a box radius other than 0.5 (film.rs:68-91, boxf.rs:10-34, Q14): unweighted colour sum over the
+    neighbourhood / number of samples inside the box.  (a) against the oracle, which keeps the reference's per-sample film, with
+    paired random numbers, for all three samplers; (b) exactly, against the same reconstruction done in numpy on the GPU's own
+    radius-0.5 frame with the closed-form recurrence offsets (isolates k_resolve_box from path noise)."""
+    fs, sc, osc = scene_pair("c1b")
+    w, h = 72, 40
+    for sampler, div, spp in (("recurrence", (1, 1), 6), ("random", (1, 1), 5), ("jittered", (3, 2), 6)):
+        kw = dict(spp=spp, seed=4, sampler=sampler, div=div, filter_radius=radius)
+        gi, g8, gst = sc.render(w, h, want_rgb8=True, **kw)
+        oi, o8, ost = osc.render(w, h, want_rgb8=True, rng_mode=1, **kw)
+        assert gst["paths"] == ost["paths"] == w * h * spp
+        fin = np.isfinite(oi).all(-1)
+        assert np.array_equal(fin, np.isfinite(gi).all(-1))          # pixels without a sample inside the box are inf / NaN on both sides
+        rel = (np.abs(gi - oi) / (np.abs(oi) + 1e-3))[fin]
+        assert float((rel.max(-1) < 2e-3).mean()) >= 0.97, (sampler, float((rel.max(-1) < 2e-3).mean()))
+        assert (np.abs(g8.astype(int) - o8.astype(int)) <= 1).mean() >= 0.97
+        assert np.array_equal(g8[fin], np.clip(gi[fin] * np.float32(255.0), 0, 255).astype(np.uint8))
+    spp = 6
+    base, _ = sc.render(w, h, spp=spp, seed=4)                       # own-pixel means: sums = mean * spp
+    got, _ = sc.render(w, h, spp=spp, seed=4, filter_radius=radius)
+    ox, oy = _r2_offsets(w, h, spp)
+    R = int(np.ceil(np.float32(radius) - np.float32(0.5)))
+    num, cnt = np.zeros((h, w, 3), np.float64), np.zeros((h, w), np.float64)
+    sums = base.astype(np.float64) * spp
+    fx, fy = ox.reshape(h, w, spp) - np.float32(0.5), oy.reshape(h, w, spp) - np.float32(0.5)
+    for j in range(-R, R + 1):
+        for i in range(-R, R + 1):
+            ys, xs = slice(max(0, -j), min(h, h - j)), slice(max(0, -i), min(w, w - i))          # output pixels whose neighbour (x+i, y+j) exists
+            yn, xn = slice(max(0, -j) + j, min(h, h - j) + j), slice(max(0, -i) + i, min(w, w - i) + i)
+            num[ys, xs] += sums[yn, xn]
+            inside = (np.abs(np.float32(i) + fx[yn, xn]) <= np.float32(radius)) & (np.abs(np.float32(j) + fy[yn, xn]) <= np.float32(radius))
+            cnt[ys, xs] += inside.sum(-1)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        want = num / cnt[..., None]
+    ok = cnt > 0
+    assert np.allclose(got[ok], want[ok], rtol=2e-6, atol=1e-7)
+    assert not np.isfinite(got[~ok]).any()
+
+
+@pytest.mark.parametrize("name", ["c1", "c2", "c4", "c5"])
+def test_debug_normal_aov_matches_oracle(scene_pair, name):
+    """The reference's `debug_normal` feature (pt.rs:113-118): first-hit interpolated normal as a colour.  Paired sub-pixel offsets:
+    the two images are the same function of the same camera rays."""
+    from spt import abi
+    fs, sc, osc = scene_pair(name)
+    w, h, spp = 192, 108, 4
+    gi, gst = sc.render(w, h, spp=spp, seed=2, flags=abi.RENDER_DEBUG_NORMAL)
+    oi, ost = osc.render(w, h, spp=spp, seed=2, rng_mode=1, debug_normal=True)
+    assert gst["paths"] == ost["paths"] == w * h * spp and gst["shadow_rays"] == 0 and gst["ext_rays"] == gst["paths"]
+    d = np.abs(gi - oi).max(-1)
+    assert (d < 1e-4).mean() >= 0.999, float((d < 1e-4).mean())      # the rest: a silhouette sample that grazes another triangle
+    assert 0.0 <= gi.min() and gi.max() <= 1.0 + 1e-6 or fs.env is not None
+    again, _ = sc.render(w, h, spp=spp, seed=2, flags=abi.RENDER_DEBUG_NORMAL, pool_size=4096)
+    assert np.array_equal(gi, again)
+
+
 def test_errors_are_reported_not_swallowed(ctx, scene_pair):
     from spt import abi, core, loader, scenes
     fs, sc, _ = scene_pair("c1")
     with pytest.raises(abi.SptError, match="radius"):
-        sc.render(32, 32, spp=1, filter_radius=1.5)
+        sc.render(32, 32, spp=1, filter_radius=4.0)
+    with pytest.raises(abi.SptError, match="radius"):
+        sc.render(32, 32, spp=1, filter_radius=0.0)
+    with pytest.raises(abi.SptError, match="consecutive"):
+        sc.render(32, 32, spp=8, spp_range=(0, 2))
+        sc.render(32, 32, spp=8, spp_range=(4, 2), flags=abi.RENDER_ACCUMULATE, filter_radius=1.0)
     with pytest.raises(abi.SptError, match="camera"):
         sc.render(32, 32, spp=1, camera=3)
     with pytest.raises(abi.SptError):
@@ -264,6 +389,16 @@ def test_errors_are_reported_not_swallowed(ctx, scene_pair):
     with pytest.raises(abi.SptError, match="no light"):
         nolight.render(16, 16, spp=1)
     nolight.close()
+    # malformed descriptors are refused by spt_scene_create instead of reading out of bounds on the device
+    for field, value, msg in (("light_sampler", 7, "light_sampler"), ("env_light_index", 5, "env_light_index")):
+        bad = loader.load_scene(scenes.c1(), scenes.BASE_PATH)
+        setattr(bad, field, value)
+        with pytest.raises(abi.SptError, match=msg):
+            core.Scene(ctx, bad)
+    bad = loader.load_scene(scenes.c2(), scenes.BASE_PATH)
+    bad.materials[3]["rough_chan"] = 9
+    with pytest.raises(abi.SptError, match="rough_chan"):
+        core.Scene(ctx, bad)
 
 
 @pytest.mark.parametrize("name", ["c2", "c4"])
@@ -281,11 +416,14 @@ def test_device_built_bvh_is_interchangeable_with_the_host_built_one(ctx, monkey
     hi, di = host.info(), dev.info()
     assert hi["blas_on_device"] == 0 and di["blas_on_device"] == len(fs.meshes) and di["triangles"] == hi["triangles"]
     assert di["seconds_bvh"] > 0 and di["seconds_create"] >= di["seconds_bvh"]
+    import orc
+    osc = orc.OracleScene(fs, fix_q1=True)
     prim = R.primary_rays(fs, 256, 144)
     for batch in (prim, R.bounce_rays(prim, host.trace(prim)), R.incoherent_rays(fs, 1 << 15)):
         a, b = host.trace(batch), dev.trace(batch)
         cmp_ = R.compare_hits(a, b)
         assert cmp_["match_rate"] == 1.0 and cmp_["bit_exact_t"] == 1.0 and cmp_["tie_rate"] < 1e-3, cmp_
+        _assert_hits(R.compare_hits(osc.trace(batch)[0], b))    # and the device-built scene against the ORACLE, not only against CUDA
     shadow = R.incoherent_rays(fs, 1 << 15, finite_tmax=True)
     assert np.array_equal(host.occluded(shadow), dev.occluded(shadow))
     ia, _ = host.render(160, 96, spp=8, seed=11)
