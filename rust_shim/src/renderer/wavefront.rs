@@ -58,6 +58,8 @@ impl RendererT for WavefrontPathTracer {
             world_size: 1,
             pool_size: 0,
             flags: 0,
+            spp_first: 0, // the whole frame in one call (progressive passes: see SPT_RENDER_ACCUMULATE in spt.h)
+            spp_count: 0,
         };
         let n = (config.width * config.height * 3) as usize;
         let (mut mean, mut rgb8) = (vec![0f32; n], vec![0u8; n]);

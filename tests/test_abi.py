@@ -102,3 +102,36 @@ def test_rust_ffi_is_in_sync():
         assert f"pub fn {sym}(" in text, sym
     for st in ("SptSceneDesc", "SptRenderDesc", "SptStats", "SptRay", "SptHit", "SptTextureDesc", "SptBxdfQuery", "SptBxdfResult"):
         assert f"pub struct {st} {{" in text, st
+    # every struct LITERAL the hand-written shim sources and INTEGRATION.md build must name exactly the fields of the generated
+    # #[repr(C)] struct, in order (Rust has no defaults for a plain struct literal: a missing field does not compile)
+    import re
+    fields = {m.group(1): re.findall(r"pub (\w+):", m.group(2)) for m in re.finditer(r"pub struct (\w+) \{(.*?)\n\}", text, flags=re.S)}
+    def literal_fields(body):  # field names of a struct literal body: `name: expr,` or shorthand `name,` at nesting depth 0
+        body = re.sub(r"//.*", "", body)
+        while True:  # drop nested (...) [...] {...} and closure bars |..|
+            flat = re.sub(r"\([^()\[\]{}]*\)|\[[^()\[\]{}]*\]|\{[^()\[\]{}]*\}|\|[^|]*\|", "", body)
+            if flat == body:
+                break
+            body = flat
+        out = []
+        for item in body.split(","):
+            item = item.replace("::", "__").strip()
+            if item:
+                out.append(item.split(":")[0].strip())
+        return out
+
+    checked = 0
+    for rel in ("rust_shim/src/renderer/wavefront.rs", "rust_shim/src/core/flatten.rs", "INTEGRATION.md"):
+        src = open(os.path.join(ROOT, rel)).read()
+        for m in re.finditer(r"\b(Spt\w+) \{\n", src):
+            name = m.group(1)
+            depth, j = 1, m.end()
+            while depth and j < len(src):
+                depth += {"{": 1, "}": -1}.get(src[j], 0)
+                j += 1
+            body = src[m.end():j - 1]
+            if name not in fields or "pub " in body or "=>" in body or "typedef" in src[max(0, m.start() - 20):m.start()] or src[max(0, m.start() - 3):m.start()] == "-> ":
+                continue
+            assert sorted(literal_fields(body)) == sorted(fields[name]), (rel, name, literal_fields(body), fields[name])
+            checked += 1
+    assert checked >= 2
