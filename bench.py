@@ -71,9 +71,38 @@ def workload(args):
     return cfg, w, h, spp
 
 
+def cpu_sample_size(w, h, cores):
+    """Bounded sample of the workload for the CPU arm: the same scene, camera, aspect ratio, depth and sampler at reduced
+    resolution, with the height a multiple of the reference's thread count.  PathTracer::render cuts the image into
+    2 x cores contiguous row bands of height / threads rows and gives the LAST band the remainder (renderer/util.rs:6-19),
+    and its wall time is that of the slowest band: a sample whose height is not a multiple of the thread count leaves a
+    third of the rows on one thread (round 1 sampled 160 x 90 on 32 threads: 2 rows per band, 28 on the last) and
+    measures that thread, not the machine.  At the real sizes the bands are 33 rows (last: 57) of 1080; here 4 rows each."""
+    threads = 2 * cores
+    sh = min(h, 4 * threads)
+    sh -= sh % threads if sh >= threads else 0
+    sw = max(16, int(round(sh * w / h)))
+    return sw, max(1, sh), threads
+
+
+def cpu_run(osc, sw, sh, spp, seconds, seed=1):
+    """Reference-faithful render (oracle rng_mode 0: per-thread streams and sampler state, 2 x cores row bands) of about `seconds`."""
+    t = time.time(); _, st = osc.render(sw, sh, spp=1, rng_mode=0); probe = time.time() - t
+    sspp = int(max(1, min(spp, seconds / max(probe, 1e-6))))
+    t = time.time(); _, st = osc.render(sw, sh, spp=sspp, rng_mode=0, seed=seed); dt = time.time() - t
+    return st, dt, sspp
+
+
+def band_note(sh, threads):
+    t = max(1, min(threads, sh))
+    per = sh // t
+    return f"{t} threads x {per} rows per band (last band {sh - per * (t - 1)} rows)"
+
+
 def run_reference(args):
     """The reference arm: the reference's own CPU algorithm (oracle restatement — the Rust binary cannot be built here)
-    on the box's host cores, reference-faithful mode (its BVH, its per-thread RNG/sampler discipline, 2 x cores threads)."""
+    on the box's host cores, reference-faithful mode (its BVH incl. Q1/Q2, its per-thread RNG/sampler discipline, 2 x cores
+    threads on contiguous row bands)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -84,27 +113,31 @@ def run_reference(args):
     fs = scenes.load(args.workload)
     osc = orc.OracleScene(fs)
     cores = os.cpu_count() or 1
-    # bounded sample of the same workload: same scene/camera/depth/sampler at reduced resolution and spp, sized by a probe
-    sw, sh = max(16, w // 12), max(9, h // 12)
-    t = time.time(); _, st = osc.render(sw, sh, spp=1, rng_mode=0); probe = time.time() - t
-    per_path = probe / max(1, st["paths"])
-    sspp = int(max(1, min(spp, args.ref_seconds / max(per_path * sw * sh, 1e-9))))
-    for _ in range(args.warmup if args.warmup < 2 else 1):
-        osc.render(sw, sh, spp=max(1, sspp // 8), rng_mode=0)
+    sw, sh, threads = cpu_sample_size(w, h, cores)
+    st, probe_dt, sspp = cpu_run(osc, sw, sh, spp, args.ref_seconds)           # also the warm-up
     times, paths, rays = [], 0, 0
     for k in range(args.steps):
         t = time.time(); _, st = osc.render(sw, sh, spp=sspp, rng_mode=0, seed=k + 1); times.append(time.time() - t)
         paths += st["paths"]; rays += st["ext_rays"] + st["shadow_rays"] + st["probe_rays"]
     total = sum(times)
     v = paths / total / 1e6
-    sample = f"{args.workload} scene at {sw}x{sh} @ {sspp} spp per step (full config: {w}x{h} @ {spp} spp), reference BVH + per-thread RNG, {2 * cores} threads"
+    # the same algorithm on the checker's BVH (oracle fix_q1: the evidently intended bucket rule): how much of the distance to the
+    # GPU number is the reference's degenerate tree (Q1: ~600x the triangle tests per ray on the bunny scenes)
+    fst, fdt, fspp = cpu_run(orc.OracleScene(fs, fix_q1=True), sw, sh, spp, min(args.ref_seconds, 8.0))
+    sample = (f"{args.workload} scene at {sw}x{sh} @ {sspp} spp per step (full config: {w}x{h} @ {spp} spp), reference BVH (Q1/Q2) + per-thread RNG, "
+              + band_note(sh, threads))
     print(json.dumps({
         "impl": "reference", "metric": "Mpaths/s", "value": v, "unit": "Mpaths/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {w}x{h} @ {spp} spp, max_depth 8", "sampler": "recurrence"},
+        "config": {"workload": f"{args.workload}: {w}x{h} @ {spp} spp, max_depth 8", "sampler": "recurrence",
+                   "same_config_note": "same scene / camera / aspect / depth / sampler as the GPU arm; resolution and spp reduced to a bounded sample (Mpaths/s is resolution- and spp-invariant up to band balance, which the sample keeps even)"},
         "mrays_per_s": rays / total / 1e6,
         "cpu_baseline": {"value": v, "unit": "Mpaths/s", "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline_fixed_bvh": {"value": fst["paths"] / fdt / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "port",
+                                   "sample": f"same sample @ {fspp} spp on the checker BVH (oracle fix_q1: intended SAH bucket rule, identical hits), {fdt:.1f} s",
+                                   "tris_per_ray": fst["tris_tested"] / max(1, fst["ext_rays"] + fst["shadow_rays"])},
+        "tris_per_ray": st["tris_tested"] / max(1, st["ext_rays"] + st["shadow_rays"]),
         "e2e": {"value": v, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
 
@@ -122,6 +155,7 @@ def main():
     ap.add_argument("--pool", type=int, default=0)
     ap.add_argument("--ref-seconds", type=float, default=8.0, help="CPU seconds per reference/cpu_baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the converged-image parity block (about 30 s of CPU oracle)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -303,15 +337,23 @@ def main():
     if world == 1 and not args.no_cpu_baseline:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import orc
-        osc = orc.OracleScene(fs)
         cores = os.cpu_count() or 1
-        sw, sh = max(16, w // 12), max(9, h // 12)
-        t = time.time(); _, st = osc.render(sw, sh, spp=1, rng_mode=0); probe_t = time.time() - t
-        sspp = int(max(1, min(spp, 15.0 / max(probe_t, 1e-6))))
-        t = time.time(); _, st = osc.render(sw, sh, spp=sspp, rng_mode=0); dt = time.time() - t
+        sw, sh, threads = cpu_sample_size(w, h, cores)
+        st, dt, sspp = cpu_run(orc.OracleScene(fs), sw, sh, spp, 15.0)
         out["cpu_baseline"] = {"value": st["paths"] / dt / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "port",
-                               "sample": f"{args.workload} scene at {sw}x{sh} @ {sspp} spp ({st['paths']} paths, {dt:.1f} s), reference BVH + per-thread RNG, {2 * cores} threads",
-                               "mrays_per_s": (st["ext_rays"] + st["shadow_rays"] + st["probe_rays"]) / dt / 1e6}
+                               "sample": f"{args.workload} scene at {sw}x{sh} @ {sspp} spp ({st['paths']} paths, {dt:.1f} s), reference BVH (Q1/Q2) + per-thread RNG, " + band_note(sh, threads),
+                               "mrays_per_s": (st["ext_rays"] + st["shadow_rays"] + st["probe_rays"]) / dt / 1e6,
+                               "tris_per_ray": st["tris_tested"] / max(1, st["ext_rays"] + st["shadow_rays"])}
+        fst, fdt, fspp = cpu_run(orc.OracleScene(fs, fix_q1=True), sw, sh, spp, 8.0)
+        out["cpu_baseline_fixed_bvh"] = {"value": fst["paths"] / fdt / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "port",
+                                         "sample": f"same sample @ {fspp} spp ({fdt:.1f} s) on the checker BVH (oracle fix_q1: the intended SAH bucket rule, identical hits): the algorithm-equal CPU line",
+                                         "tris_per_ray": fst["tris_tested"] / max(1, fst["ext_rays"] + fst["shadow_rays"])}
+    if world == 1 and not args.no_parity:
+        # converged-image parity of this workload against the reference-faithful oracle (the checker; outside every timed region)
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import parity_stats
+        if args.workload in parity_stats.CONVERGED:
+            out["parity"] = parity_stats.converged_parity(sc, fs, args.workload, check_one_call=False)
     print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()

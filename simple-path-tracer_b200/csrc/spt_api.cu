@@ -27,6 +27,7 @@ int fail(int code, const std::string& m) { g_err = m; return code; }
 struct DevBuf { // one device allocation + the pinned staging copy used by spt_scene_upload
   void* d = nullptr; void* h = nullptr; size_t bytes = 0;
   const void* src = nullptr; // big arrays are not staged: they are copied straight from the HostScene vector the scene keeps
+  bool in_arena = false;     // d points into SptScene::hot_arena (not freed by itself)
 };
 
 } // namespace
@@ -39,6 +40,8 @@ struct SptScene {
   DScene ds{};
   std::vector<DevBuf> bufs;
   std::vector<DCamera> cameras;
+  // the arrays traversal reads (nodes, tris, tlas_inst, inst) live in ONE allocation, so that one L2 access-policy window can cover them
+  char* hot_arena = nullptr; size_t hot_bytes = 0, hot_used = 0; bool l2_window = false;
   // render-time buffers, grown on demand and reused across spt_render calls
   void* pool_mem = nullptr; size_t pool_bytes = 0; int pool_n = 0;
   long long* film = nullptr; size_t film_px = 0; // film_px = allocated pixels
@@ -61,9 +64,10 @@ struct SptScene {
 namespace {
 
 template <typename T>
-int upload(SptScene* s, const std::vector<T>& v, const T** dptr, bool kept = true) { // kept: v lives as long as the scene (a HostScene member)
+int upload(SptScene* s, const std::vector<T>& v, const T** dptr, bool kept = true, bool hot = false) { // kept: v lives as long as the scene (a HostScene member)
   DevBuf b; b.bytes = std::max<size_t>(sizeof(T), v.size() * sizeof(T));
-  CU(cudaMalloc(&b.d, b.bytes));
+  if (hot && s->hot_arena && s->hot_used + b.bytes <= s->hot_bytes) { b.d = s->hot_arena + s->hot_used; b.in_arena = true; s->hot_used += (b.bytes + 255) & ~(size_t)255; }
+  else CU(cudaMalloc(&b.d, b.bytes));
   const size_t used = v.size() * sizeof(T);
   s->bufs.push_back(b); // owned by the scene from here on: spt_scene_destroy releases it on every later failure
   DevBuf& o = s->bufs.back();
@@ -131,17 +135,24 @@ int32_t spt_scene_create(SptContext* ctx, const SptSceneDesc* desc, SptScene** o
   memset(&d, 0, sizeof(d));
   int st;
 #define UP(vec, field) if ((st = upload(s, vec, &d.field)) != SPT_OK) { spt_scene_destroy(s); return st; }
+#define UPH(vec, field) if ((st = upload(s, vec, &d.field, true, true)) != SPT_OK) { spt_scene_destroy(s); return st; }
   {
+    auto al = [](size_t b) { return (std::max<size_t>(b, 16) + 255) & ~(size_t)255; };
+    s->hot_bytes = al(h.nodes.size() * sizeof(spt::CwNode)) + al(h.tlas_inst.size() * sizeof(int32_t)) + al(h.inst.size() * sizeof(DInstance)) +
+                   al(h.spheres.size() * sizeof(float4)) + al(h.tris.size() * sizeof(float4));
+    if (cudaMalloc(&s->hot_arena, s->hot_bytes) != cudaSuccess) { cudaGetLastError(); s->hot_arena = nullptr; s->hot_bytes = 0; } // fall back to separate allocations
     std::vector<float4> nodes4(h.nodes.size() * 5);
     if (!h.nodes.empty()) memcpy(nodes4.data(), h.nodes.data(), h.nodes.size() * sizeof(spt::CwNode));
-    if ((st = upload(s, nodes4, &d.nodes, false)) != SPT_OK) { spt_scene_destroy(s); return st; }
+    if ((st = upload(s, nodes4, &d.nodes, false, true)) != SPT_OK) { spt_scene_destroy(s); return st; }
   }
-  UP(h.tris, tris); UP(h.shade_tris, shade_tris); UP(h.inst_mat, inst_mat); UP(h.tlas_inst, tlas_inst); UP(h.inst, inst); UP(h.inst_shade, inst_shade); UP(h.spheres, spheres);
+  UPH(h.tlas_inst, tlas_inst); UPH(h.inst, inst); UPH(h.spheres, spheres); UPH(h.tris, tris); // nodes first: a window smaller than the arena keeps the tree
+  UP(h.shade_tris, shade_tris); UP(h.inst_mat, inst_mat); UP(h.inst_shade, inst_shade);
   UP(h.meshes, meshes); UP(h.verts, verts); UP(h.indices, indices); UP(h.surfaces, surfaces); UP(h.materials, materials);
   UP(h.textures, textures); UP(h.mips, mips); UP(h.texels, texels); UP(h.mediums, mediums); UP(h.lights, lights);
   UP(h.light_prob, light_prob); UP(h.light_alias, light_alias); UP(h.inst_light, inst_light); UP(h.ss_cdf, ss_cdf);
   if (h.env_w > 0) { UP(h.env_tex, env_tex); UP(h.env_alias, env_alias); }
 #undef UP
+#undef UPH
   for (int c = 0; c < 3; c++) d.env_scale[c] = h.env_scale[c];
   d.env_w = h.env_w; d.env_h = h.env_h;
   d.n_lights = (int32_t)h.lights.size(); d.light_sampler = h.light_sampler; d.env_light_index = h.env_light_index;
@@ -167,6 +178,23 @@ int32_t spt_scene_create(SptContext* ctx, const SptSceneDesc* desc, SptScene** o
   CUS(cudaMalloc(&s->ctr, sizeof(DevCounters))); CUS(cudaMalloc(&s->batch_next, SPT_BATCH_CURSORS * sizeof(uint32_t)));
   CUS(cudaMallocHost(&s->h_ctr, sizeof(DevCounters)));
 #undef CUS
+  // Optional (SPT_L2_PERSIST=1): an L2 persisting access-policy window over the traversal arrays on the streams that run the
+  // traversal kernels, so that the path pool streaming through the same L2 cannot evict the BVH.  Measured: see profiles/README.md.
+  if (const char* e = getenv("SPT_L2_PERSIST")) if (atoi(e) > 0 && s->hot_arena) {
+    int max_win = 0, max_persist = 0;
+    cudaDeviceGetAttribute(&max_win, cudaDevAttrMaxAccessPolicyWindowSize, ctx->device);
+    cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, ctx->device);
+    const size_t win = std::min<size_t>(std::min<size_t>(s->hot_used, (size_t)max_win), (size_t)max_persist);
+    if (win > 0 && cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, win) == cudaSuccess) {
+      cudaStreamAttrValue av; memset(&av, 0, sizeof(av));
+      av.accessPolicyWindow.base_ptr = s->hot_arena; av.accessPolicyWindow.num_bytes = win; av.accessPolicyWindow.hitRatio = 1.0f;
+      av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting; av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+      bool ok = cudaStreamSetAttribute(s->stream, cudaStreamAttributeAccessPolicyWindow, &av) == cudaSuccess;
+      for (int i = 0; i < 3; i++) ok = ok && cudaStreamSetAttribute(s->aux[i], cudaStreamAttributeAccessPolicyWindow, &av) == cudaSuccess;
+      s->l2_window = ok;
+    }
+    cudaGetLastError();
+  }
   s->hs.seconds_create = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_create).count();
   *out = s;
   return SPT_OK;
@@ -196,7 +224,8 @@ int32_t spt_scene_info(const SptScene* s, SptSceneInfo* out) {
 int32_t spt_scene_destroy(SptScene* s) {
   if (!s) return SPT_OK;
   cudaSetDevice(s->ctx->device);
-  for (DevBuf& b : s->bufs) { cudaFree(b.d); if (b.h) cudaFreeHost(b.h); }
+  for (DevBuf& b : s->bufs) { if (!b.in_arena) cudaFree(b.d); if (b.h) cudaFreeHost(b.h); }
+  cudaFree(s->hot_arena);
   cudaFree(s->pool_mem); cudaFree(s->film); cudaFree(s->ctr); cudaFree(s->batch_next); cudaFree(s->tiles);
   cudaFree(s->out_mean); cudaFree(s->out_rgb8); cudaFree(s->stage_rays); cudaFree(s->stage_out);
   if (s->h_ctr) cudaFreeHost(s->h_ctr);

@@ -32,7 +32,9 @@ struct TravCounters { // only maintained by the COUNT instantiations
   uint32_t busy, pop, node, inst, tri, w_rounds, w_pop, w_node, w_inst, w_tri;
 };
 
+#ifndef SPT_SSTACK
 #define SPT_SSTACK 16       // stack entries per thread in shared memory
+#endif
 #ifndef SPT_WORLD_STASH
 #define SPT_WORLD_STASH 1   // 1: while a lane is inside a BLAS its world-space ray lives in shared memory, not in 10 registers
 #endif
