@@ -56,7 +56,13 @@ struct TravCounters { // only maintained by the COUNT instantiations
 #define SPT_INST_UNIFORM_SETUP 1 // 1: the object-space ray setup of an instance visit runs for small meshes too (no divergent branch)
 #endif
 #ifndef SPT_FETCH_MIN_IDLE
-#define SPT_FETCH_MIN_IDLE 6 // refill the warp once this many lanes are without a ray
+#define SPT_FETCH_MIN_IDLE 3 // refill the warp once this many lanes are without a ray (6 before the pop stage moved to the end of the round)
+#endif
+#ifndef SPT_POP_END
+#define SPT_POP_END 1        // 1: the pop stage closes the round instead of opening it (see trace_persistent)
+#endif
+#ifndef SPT_TRI_HELP
+#define SPT_TRI_HELP 1       // 1: ONE triangle pass per round in which lanes without triangle work test the second pending triangle of lanes that have two
 #endif
 
 SPT_D uint32_t sext_s8x4(uint32_t x) { uint32_t v; asm("prmt.b32 %0, %1, 0x0, 0x0000BA98;" : "=r"(v) : "r"(x)); return v; }
@@ -390,12 +396,19 @@ SPT_D bool traverse(const DScene& sc, float3 ow, float3 dw, float tmin, HitRec& 
 //
 // Every round the whole warp passes through the same fixed chain of stages, each executed once by all the lanes that
 // have that kind of work pending, in the order a single ray needs them:
-//   refill -> pop (stack / leave BLAS / finish) -> node step -> instance visit -> triangle test (x SPT_TRI_PER_ROUND)
+//   refill -> node step -> instance visit -> triangle pass -> pop (stack / leave BLAS / finish)
 // so a lane can advance through several stages in one round, no lane ever waits for another lane's leaf work, and
 // lanes doing the same kind of work execute it together instead of drifting apart under independent thread scheduling.
+// The pop stage CLOSES the round (SPT_POP_END): a ray whose last test ran in this round finds its stack empty now and gives its
+// lane back for the next round's refill; opening the round with it (round 1) cost every ray one whole round at the end of its life
+// in which its lane did nothing else (tools/trav_sim.py: 4.6 -> 3.6 lane-rounds per ray on C2).
+// Triangle pass (SPT_TRI_HELP): every lane with pending triangles tests its next one; lanes that have NO triangle work in this round
+// (a third to two thirds of the warp) each take the second pending triangle of the i-th lane that has two or more — the ray goes over
+// by shuffles, the result comes back the same way and is applied after the owner's own, i.e. in the order a sequential loop would
+// (same hit on equal-t ties).  One such pass does the work of the two triangle stages it replaces.
 // A lane drains its pending primitive group before it takes its next node step (same order as a depth-first loop).
 #ifndef SPT_TRI_PER_ROUND
-#define SPT_TRI_PER_ROUND 2
+#define SPT_TRI_PER_ROUND (SPT_TRI_HELP ? 1 : 2)
 #endif
 #ifndef SPT_INST_PER_ROUND
 #define SPT_INST_PER_ROUND 1
@@ -409,6 +422,9 @@ SPT_D bool traverse(const DScene& sc, float3 ow, float3 dw, float tmin, HitRec& 
 template <bool ANY, bool COUNT, class Src>
 SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCounters& cnt) {
   __shared__ uint2 s_stack[SPT_SSTACK + SPT_WSTASH][SPT_TRAV_BLOCK];
+#if SPT_TRI_HELP
+  __shared__ uint32_t s_pair[SPT_TRAV_BLOCK / 32][64]; // per warp: the lane pairing of the triangle pass
+#endif
   uint2 l_stack[SPT_LSTACK];
   TravStack st; st.sh = &s_stack[0][threadIdx.x]; st.lo = l_stack;
   const uint32_t total = src.total(), lane = threadIdx.x & 31u, FULL = 0xffffffffu;
@@ -453,12 +469,14 @@ SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCoun
     }
     bool fin = false;
     if (COUNT) { cnt.busy += has ? 1u : 0u; if (lane == 0) cnt.w_rounds++; }
+#if !SPT_POP_END
     // ---- pop: nothing pending -> leave the BLAS / next stack entry / ray finished
     {
       const bool p = has && !trav_has_node(T) && !trav_has_leaf(T);
       if (COUNT) { const uint32_t m = __ballot_sync(FULL, p); cnt.pop += p ? 1u : 0u; if (lane == 0 && m) cnt.w_pop++; }
       if (p) fin = trav_pop(T, st);
     }
+#endif
 #if SPT_STAGE_ORDER == 1
     if (has && !fin && trav_has_leaf(T) && T.cur_inst < 0) fin = trav_inst<ANY, COUNT>(sc, T, st, cnt);
 #endif
@@ -477,12 +495,78 @@ SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCoun
       if (p) fin = trav_inst<ANY, COUNT>(sc, T, st, cnt);
     }
     // ---- triangle tests (BLAS leaf / small mesh)
+#if SPT_TRI_HELP
+#pragma unroll
+    for (int k = 0; k < SPT_TRI_PER_ROUND; k++) {
+      const bool own = has && !fin && trav_has_leaf(T) && T.cur_inst >= 0;
+      const uint32_t m_own = __ballot_sync(FULL, own);
+      if (m_own != 0u) { // warp-uniform
+        uint32_t k1 = 0, k2 = 0;
+        if (own) { k1 = bfind_u32(T.tg.y); T.tg.y &= ~(1u << k1); }
+        const bool rich = own && T.tg.y != 0u;                 // a second triangle is pending
+        if (rich) k2 = bfind_u32(T.tg.y);
+        const uint32_t m_rich = __ballot_sync(FULL, rich), m_poor = ~m_own, lt = (1u << lane) - 1u;
+        const uint32_t n_pairs = min(__popc(m_rich), __popc(m_poor)); // the i-th lane without triangle work helps the i-th rich lane
+        const uint32_t r_rich = __popc(m_rich & lt), r_poor = __popc(m_poor & lt);
+        const bool helped = rich && r_rich < n_pairs, helper = !own && r_poor < n_pairs;
+        uint32_t* map = s_pair[threadIdx.x >> 5];              // [0..31]: rank -> rich lane, [32..63]: rank -> helper lane
+        if (n_pairs) {
+          if (helped) map[r_rich] = lane;
+          if (helper) map[32 + r_poor] = lane;
+          __syncwarp();
+        }
+        const uint32_t from = helper ? map[r_poor] : lane;     // whose ray this lane tests
+        const uint32_t back = helped ? map[32 + r_rich] : lane; // who tests this lane's second triangle
+        if (helped) T.tg.y &= ~(1u << k2);
+        float3 o = T.r.o, d = T.r.d;
+        uint32_t pidx = T.tg.x + k1;
+        if (n_pairs) { // hand the rays (and the second triangle's index) over; own lanes read themselves
+          const uint32_t second = T.tg.x + k2;
+          o.x = __shfl_sync(FULL, T.r.o.x, from); o.y = __shfl_sync(FULL, T.r.o.y, from); o.z = __shfl_sync(FULL, T.r.o.z, from);
+          d.x = __shfl_sync(FULL, T.r.d.x, from); d.y = __shfl_sync(FULL, T.r.d.y, from); d.z = __shfl_sync(FULL, T.r.d.z, from);
+          const uint32_t p2 = __shfl_sync(FULL, second, from);
+          if (helper) pidx = p2;
+          __syncwarp(); // map is rewritten by the next pass / round
+        }
+        float t = __int_as_float(0x7fc00000), v = 0.f, w = 0.f; int tid = -1; // NaN = no hit: fails t > tmin for every tmin
+        if (own || helper) {
+          if (COUNT) cnt.tris++;
+          float th;
+          if (tri_test(sc.tris, pidx, o, d, th, v, w, tid)) t = th;
+        }
+        if (COUNT) { const uint32_t m = __ballot_sync(FULL, own || helper); cnt.tri += (own || helper) ? 1u : 0u; if (lane == 0 && m) cnt.w_tri++; }
+        float t2 = __int_as_float(0x7fc00000), v2 = 0.f, w2 = 0.f; int tid2 = -1;
+        if (n_pairs) { // results of the helpers back to the owners
+          t2 = __shfl_sync(FULL, t, back); v2 = __shfl_sync(FULL, v, back); w2 = __shfl_sync(FULL, w, back); tid2 = __shfl_sync(FULL, tid, back);
+        }
+        if (own) { // the owner's own triangle first, then the helped one: the order of the sequential loop (triangle.rs:177-187)
+          if (t > T.tmin && t < T.hit.t) {
+            if (ANY) { T.hit.inst = 0; fin = true; }
+            else { T.hit.t = t; T.hit.u = v; T.hit.v = w; T.hit.prim = tid; T.hit.tri = (int)(T.tg.x + k1); T.hit.inst = T.cur_inst; }
+          }
+          if (helped && t2 > T.tmin && t2 < T.hit.t) {
+            if (ANY) { T.hit.inst = 0; fin = true; }
+            else { T.hit.t = t2; T.hit.u = v2; T.hit.v = w2; T.hit.prim = tid2; T.hit.tri = (int)(T.tg.x + k2); T.hit.inst = T.cur_inst; }
+          }
+        }
+      }
+    }
+#else
 #pragma unroll
     for (int k = 0; k < SPT_TRI_PER_ROUND; k++) {
       const bool p = has && !fin && trav_has_leaf(T) && T.cur_inst >= 0;
       if (COUNT) { const uint32_t m = __ballot_sync(FULL, p); cnt.tri += p ? 1u : 0u; if (lane == 0 && m) cnt.w_tri++; }
       if (p) fin = trav_tri<ANY, COUNT>(sc, T, cnt);
     }
+#endif
+#if SPT_POP_END
+    // ---- pop: nothing pending -> leave the BLAS / next stack entry / ray finished
+    {
+      const bool p = has && !fin && !trav_has_node(T) && !trav_has_leaf(T);
+      if (COUNT) { const uint32_t m = __ballot_sync(FULL, p); cnt.pop += p ? 1u : 0u; if (lane == 0 && m) cnt.w_pop++; }
+      if (p) fin = trav_pop(T, st);
+    }
+#endif
     if (fin) { src.store(idx, T.hit); has = false; }
   }
 }
