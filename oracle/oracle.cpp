@@ -568,6 +568,38 @@ extern "C" int32_t orc_light_probs(OrcScene* S, float* out) {
   for (size_t i = 0; i < ls.lights.size(); i++) out[i] = ls.kind == 1 ? ls.alias.probability(i) : ls.num_light_inv;
   return SPT_OK;
 }
+// EnvLight::strength_dist_pdf by direction (environment.rs:52-84, :128-133): out = (r, g, b, pdf) per direction
+extern "C" int32_t orc_env_lookup(OrcScene* S, const float* dirs, int64_t n, float* out) {
+  if (!S || !S->has_env) { g_err = "scene has no environment"; return SPT_ERR_INVALID; }
+  for (int64_t i = 0; i < n; i++) {
+    Color c; float dist, pdf;
+    S->env.strength_dist_pdf(v3(dirs + 3 * i), c, dist, pdf);
+    out[4 * i] = c.r; out[4 * i + 1] = c.g; out[4 * i + 2] = c.b; out[4 * i + 3] = pdf;
+  }
+  return SPT_OK;
+}
+// medium/util.rs:1-19
+extern "C" int32_t orc_hg(float g, const float* x, int64_t n, float* phase_of_cos, float* cos_of_rand) {
+  for (int64_t i = 0; i < n; i++) { phase_of_cos[i] = henyey_greenstein(g, x[i]); cos_of_rand[i] = henyey_greenstein_cdf_inverse(g, x[i]); }
+  return SPT_OK;
+}
+// SS_CDF_TABLE (substrate.rs:187-196) as 512 (x, y) pairs, and Subsurface::sample_r (:217-228)
+extern "C" int32_t orc_ss_table(float* out_xy, const float* rand, int64_t n, float* out_r) {
+  const auto& T = ss_cdf_table();
+  if (out_xy) for (size_t i = 0; i < T.size(); i++) { out_xy[2 * i] = T[i].first; out_xy[2 * i + 1] = T[i].second; }
+  for (int64_t i = 0; i < n; i++) out_r[i] = Substrate::sample_r(rand[i]);
+  return SPT_OK;
+}
+// Intersection::calc_differential (intersection.rs:28-83).  in: t, ray o/d, normal, tangent, bitangent, aux-x o/d, aux-y o/d
+// (1 + 9 * 3 floats); out: duvdx, duvdy
+extern "C" int32_t orc_calc_differential(const float* in, float* out4) {
+  Ray ray(v3(in + 1), v3(in + 4));
+  Intersection inter; inter.t = in[0]; inter.normal = v3(in + 7); inter.tangent = v3(in + 10); inter.bitangent = v3(in + 13);
+  ray.has_aux = true; ray.aux = {v3(in + 16), v3(in + 19), v3(in + 22), v3(in + 25)};
+  inter.calc_differential(ray);
+  out4[0] = inter.duvdx.x; out4[1] = inter.duvdx.y; out4[2] = inter.duvdy.x; out4[3] = inter.duvdy.y;
+  return SPT_OK;
+}
 extern "C" int32_t orc_rng_stream(uint64_t seed, uint64_t pixel, uint64_t sample, int32_t n, float* out) {
   Rng r; r.key(seed, pixel, sample);
   for (int i = 0; i < n; i++) out[i] = r.uniform_1d();

@@ -44,6 +44,10 @@ def lib():
         L.orc_alias_table.argtypes = [vp, C.c_int32, vp, vp]
         L.orc_alias_sample.argtypes = [vp, C.c_int32, vp, C.c_int64, vp]
         L.orc_light_probs.argtypes = [vp, vp]
+        L.orc_env_lookup.argtypes = [vp, vp, C.c_int64, vp]
+        L.orc_hg.argtypes = [C.c_float, vp, C.c_int64, vp, vp]
+        L.orc_ss_table.argtypes = [vp, vp, C.c_int64, vp]
+        L.orc_calc_differential.argtypes = [vp, vp]
         L.orc_rng_stream.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_int32, vp]
         _lib = L
     return _lib
@@ -122,10 +126,42 @@ class OracleScene:
         _chk(lib().orc_bxdf_batch(self.h, q, n, r))
         return list(r)
 
+    def env_lookup(self, dirs):
+        """EnvLight::strength_dist_pdf(wi) -> [n, 4] = (r, g, b, pdf)"""
+        d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+        out = np.zeros((len(d), 4), np.float32)
+        _chk(lib().orc_env_lookup(self.h, d.ctypes.data, len(d), out.ctypes.data))
+        return out
+
     def light_probs(self):
         out = np.zeros(len(self.fs.lights), np.float32)
         _chk(lib().orc_light_probs(self.h, out.ctypes.data))
         return out
+
+
+def hg(g, x):
+    """(henyey_greenstein(g, x), henyey_greenstein_cdf_inverse(g, x)) elementwise (medium/util.rs:1-19)"""
+    x = np.ascontiguousarray(x, np.float32)
+    a, b = np.zeros_like(x), np.zeros_like(x)
+    _chk(lib().orc_hg(g, x.ctypes.data, len(x), a.ctypes.data, b.ctypes.data))
+    return a, b
+
+
+def ss_table(rand=()):
+    """(SS_CDF_TABLE as [512, 2], Subsurface::sample_r(rand)) (substrate.rs:187-228)"""
+    tab = np.zeros((512, 2), np.float32)
+    r = np.ascontiguousarray(rand, np.float32)
+    out = np.zeros_like(r)
+    _chk(lib().orc_ss_table(tab.ctypes.data, r.ctypes.data, len(r), out.ctypes.data))
+    return tab, out
+
+
+def calc_differential(t, o, d, normal, tangent, bitangent, xo, xd, yo, yd):
+    """Intersection::calc_differential (intersection.rs:28-83) -> (duvdx, duvdy)"""
+    a = np.concatenate([[t], o, d, normal, tangent, bitangent, xo, xd, yo, yd]).astype(np.float32)
+    out = np.zeros(4, np.float32)
+    _chk(lib().orc_calc_differential(a.ctypes.data, out.ctypes.data))
+    return out[:2], out[2:]
 
 
 def alias_table(props):

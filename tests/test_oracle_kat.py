@@ -241,3 +241,144 @@ def test_reference_faithful_and_keyed_modes_agree_statistically():
     a, _ = sc.render(48, 48, spp=64, rng_mode=0, seed=1)
     b, _ = sc.render(48, 48, spp=64, rng_mode=1, seed=1)
     assert abs(a.mean() / b.mean() - 1) < 0.03
+
+
+# ---- known-answer tests added in round 2: pieces where a mis-reading of the Rust source would be silent in both the oracle and
+# the CUDA core (they share the reading).  Every expected value below is worked out by hand / in float64 from the cited lines.
+
+def test_env_light_pdf_worked_example_q7(tmp_path):
+    """EnvLight::new + strength_dist_pdf (environment.rs:18-84) on a 2x2 grey map [[1, 3], [2, 2]], scale (1, 2, 0.5).
+    new():  theta_row = (row + 0.5) / H WITHOUT pi (Q7) -> sin(0.25), sin(0.75); prop = lum * sin; normalised.
+    lookup: x = phi / 2pi * W, x1 = round(x), x0 = x1 - 1, xt = x - x0 - 0.5 (clamped after); same in y with theta / pi * H;
+            bilinear colour; pdf = p0 * (1 - xt) * p1 * xt — a PRODUCT of the two column terms, no solid-angle Jacobian (Q7).
+    by direction: theta = acos(wi.y), phi = atan2(wi.x, wi.z) + pi."""
+    env = np.zeros((2, 2, 3), np.float32)
+    env[0, 0], env[0, 1], env[1, 0], env[1, 1] = 1.0, 3.0, 2.0, 2.0
+    np.save(tmp_path / "env.npy", env)
+    d = scenes.c1()
+    d["environment"] = {"type": "npy", "npy_file": str(tmp_path / "env.npy"), "scale": [1.0, 2.0, 0.5]}
+    sc = orc.OracleScene(_scene(d))
+    s0, s1 = math.sin(0.25), math.sin(0.75)
+    raw = np.array([1 * s0, 3 * s0, 2 * s1, 2 * s1])
+    P = raw / raw.sum()                                    # [0.066575, 0.199724, 0.366850, 0.366850]
+    assert np.allclose(P, [0.0665751, 0.1997253, 0.3668498, 0.3668498], atol=2e-6)
+    # (a) wi = (0, 0, 1): theta = pi/2 -> y = 1.0, y1 = 1, y0 = 0, yt = 0.5; phi = atan2(0, 1) + pi = pi -> x = 1.0, xt = 0.5
+    #     colour = mean of the four texels = 2; pdf = ((P00 + P10) / 2 * 0.5) * ((P01 + P11) / 2 * 0.5)
+    want_a = ((P[0] + P[2]) / 2 * 0.5) * ((P[1] + P[3]) / 2 * 0.5)
+    assert abs(want_a - 0.0153480) < 1e-6
+    # (b) wi = (0, 0.5, sqrt(3)/2): theta = pi/3 -> y = 2/3, y1 = 1, y0 = 0, yt = 1/6; phi = pi -> xt = 0.5
+    yt = 2.0 / 3.0 - 0.5
+    c0, c1 = 1 * (1 - yt) + 2 * yt, 3 * (1 - yt) + 2 * yt
+    want_b_c = 0.5 * c0 + 0.5 * c1
+    want_b = ((P[0] * (1 - yt) + P[2] * yt) * 0.5) * ((P[1] * (1 - yt) + P[3] * yt) * 0.5)
+    assert abs(want_b_c - 2.0) < 1e-12 and abs(want_b - 0.0066351) < 1e-6
+    # (c) wi = (-1, 0, 0): phi = atan2(-1, 0) + pi = pi/2 -> x = 0.5, x1 = round(0.5) = 1 (f32::round: half away from zero),
+    #     x0 = 0, xt = 0 -> the x1 column term is multiplied by xt = 0: pdf = 0 exactly (the product rule), colour = column 0
+    got = sc.env_lookup([[0, 0, 1], [0, 0.5, math.sqrt(3) / 2], [-1, 0, 0]])
+    assert np.allclose(got[0], [2.0, 4.0, 1.0, want_a], rtol=2e-5)
+    assert np.allclose(got[1], [2.0, 4.0, 1.0, want_b], rtol=2e-5)
+    assert got[2, 3] == 0.0 and np.allclose(got[2, :3], np.array([1.5, 3.0, 0.75]), rtol=2e-5)   # column 0: (1 + 2) / 2
+    # power() = avg_power * 4 pi with avg_power = sum / (W * H) (environment.rs:39, :139-141): it is light 0 of a power_is sampler
+    d["light_sampler"] = "power_is"
+    d["lights"] = [{"type": "point", "name": "p", "position": [0.0, 3.0, 0.0], "strength": [2.0, 2.0, 2.0]}]
+    probs = orc.OracleScene(_scene(d)).light_probs()
+    env_power, point_power = raw.sum() / 4 * 4 * math.pi, 2.0
+    assert np.allclose(sorted(probs), sorted([point_power / (env_power + point_power), env_power / (env_power + point_power)]), rtol=1e-5)
+
+
+def test_power_is_two_light_worked_example():
+    """PowerIsLightSampler::new (power_is.rs:19-42): props = power / sum with power = luminance(strength) for delta lights.
+    Directional (1,1,1) and point (3,3,3): props (0.25, 0.75); AliasTable::new on them: u = n * props = (0.5, 1.5), poor = 0,
+    rich = 1: u[1] -= 1 - u[0] -> 1.0, k[0] = 1.  sample(r): x = floor(2 r), y = frac(2 r): r = 0.2 -> (0, 0.4 < 0.5) -> light 0;
+    r = 0.3 -> (0, 0.6) -> k[0] = light 1; r >= 0.5 -> light 1.  So light 0 is drawn with probability 0.25 and the pdf it reports
+    is its prop 0.25 — checked end to end: a max_depth-1 render of a Lambert plane must converge to the SUM of both lights'
+    closed-form radiance whatever the probabilities are, and it only does if pdf == the frequency actually used."""
+    assert np.array_equal(orc.alias_sample([0.25, 0.75], [0.2, 0.24, 0.3, 0.49, 0.5, 0.99]), [0, 0, 1, 1, 1, 1])
+    u, k = orc.alias_table([0.25, 0.75])
+    assert np.allclose(u, [0.5, 1.0]) and list(k) == [1, 1]
+    d = scenes.c1b()
+    d["instances"] = [{"name": "floor", "primitive": "plane", "material": "lambert_blue", "scale": [50.0, 1.0, 50.0]}]  # y = 0, albedo (0.2, 0.3, 0.8)
+    d["cameras"] = {"type": "perspective", "name": "c", "eye": [0.0, 5.0, 0.0], "forward": [0.0, -1.0, 0.0], "up": [0.0, 0.0, -1.0], "fov": 20.0}
+    d["lights"] = [{"type": "directional", "name": "d", "direction": [0.0, -1.0, 0.0], "strength": [1.0, 1.0, 1.0]},
+                   {"type": "point", "name": "p", "position": [0.0, 2.0, 0.0], "strength": [3.0, 3.0, 3.0]}]
+    d["light_sampler"] = "power_is"
+    sc = orc.OracleScene(_scene(d))
+    assert np.allclose(sc.light_probs(), [0.25, 0.75], rtol=1e-6)
+    img, _ = sc.render(33, 33, spp=4096, max_depth=1, rng_mode=0, seed=5)
+    # centre pixel looks at (0, 0, 0): directional: 1 * albedo/pi * cos 0; point: 3 / r^2 * albedo/pi * 1 with r = 2 (point.rs:31-43)
+    want = np.array([0.2, 0.3, 0.8]) / math.pi * (1.0 + 3.0 / 4.0)
+    assert np.allclose(img[16, 16], want, rtol=0.03), (img[16, 16], want)
+    uni = dict(d, light_sampler="uniform")
+    img_u, _ = orc.OracleScene(_scene(uni)).render(33, 33, spp=4096, max_depth=1, rng_mode=0, seed=6)
+    assert np.allclose(img_u[16, 16], want, rtol=0.03)
+
+
+def test_calc_differential_on_an_axis_aligned_plane():
+    """Intersection::calc_differential (intersection.rs:28-83): the aux rays are intersected with the tangent plane, dp/dx and
+    dp/dy are projected on the two axes other than the dominant normal axis and the 2x2 system [tangent bitangent] duv = dp is
+    solved.  Plane z = 0, dp/du = tangent = (2, 0, 0), dp/dv = bitangent = (0, 3, 0); camera at (0, 0, 1) looking down; the
+    x aux ray leaves through (0.1, 0, 0) on the plane, the y aux ray through (0, 0.2, 0):  duv/dx = (0.05, 0), duv/dy = (0, 0.0667)."""
+    nx, ny = np.array([0.1, 0, -1.0]), np.array([0, 0.2, -1.0])
+    dx, dy = orc.calc_differential(1.0, [0, 0, 1], [0, 0, -1], [0, 0, 1], [2, 0, 0], [0, 3, 0],
+                                   [0, 0, 1], nx / np.linalg.norm(nx), [0, 0, 1], ny / np.linalg.norm(ny))
+    assert np.allclose(dx, [0.05, 0.0], atol=1e-6) and np.allclose(dy, [0.0, 0.2 / 3.0], atol=1e-6)
+    # dominant axis y (a floor): the projection takes (z, x) (intersection.rs:56-63); tangent along x, bitangent along -z
+    dx, dy = orc.calc_differential(2.0, [0, 2, 0], [0, -1, 0], [0, 1, 0], [1, 0, 0], [0, 0, -1],
+                                   [0, 2, 0], np.array([0.5, -2, 0]) / math.hypot(0.5, 2), [0, 2, 0], np.array([0, -2, 0.25]) / math.hypot(2, 0.25))
+    assert np.allclose(dx, [0.5, 0.0], atol=1e-6) and np.allclose(dy, [0.0, -0.25], atol=1e-6)
+    # a skewed frame: tangent (1, 0, 0), bitangent (1, 1, 0): dp = (0.3, 0.1, 0) = 0.2 * tangent + 0.1 * bitangent
+    dx, _ = orc.calc_differential(1.0, [0, 0, 1], [0, 0, -1], [0, 0, 1], [1, 0, 0], [1, 1, 0],
+                                  [0, 0, 1], np.array([0.3, 0.1, -1]) / np.linalg.norm([0.3, 0.1, 1]), [0, 0, 1], [0, 0, -1])
+    assert np.allclose(dx, [0.2, 0.1], atol=1e-6)
+
+
+def test_subsurface_cdf_table_and_sample_r():
+    """SS_CDF_TABLE (substrate.rs:187-196): x_i = -2 ln(1 - i/512), y_i = 1 - e^-x / 4 - 3 e^(-x/3) / 4, the CDF of the normalised
+    diffusion profile in units of d; sample_r (:217-228) inverts it by linear interpolation and returns -1 beyond the table."""
+    tab, r = orc.ss_table([0.0, 0.25, 0.5, 0.9, 0.999])
+    i = np.arange(512, dtype=np.float64)
+    x = -2.0 * np.log(1.0 - i / 512.0)
+    y = 1.0 - np.exp(-x) / 4.0 - 3.0 * np.exp(-x / 3.0) / 4.0
+    assert tab[0, 0] == 0.0 and tab[0, 1] == 0.0
+    assert np.allclose(tab[:, 0], x, rtol=1e-5, atol=1e-7) and np.allclose(tab[:, 1], y, rtol=1e-5, atol=1e-7)
+    assert abs(tab[511, 0] - 2.0 * math.log(512.0)) < 1e-4          # x_max = -2 ln(1/512) = 12.4766
+    assert abs(tab[511, 1] - (1 - (1 / 512.0) ** 2 / 4 - 0.75 * (1 / 512.0) ** (2 / 3.0))) < 1e-6   # y_max = 0.98828
+    assert np.all(np.diff(tab[:, 1]) > 0)
+    # inversion: CDF(sample_r(u)) == u up to the table's linear interpolation; u above y_max cannot be inverted -> -1
+    cdf = lambda q: 1.0 - np.exp(-q) / 4.0 - 3.0 * np.exp(-q / 3.0) / 4.0
+    assert r[0] == 0.0 and np.allclose(cdf(r[1:4].astype(np.float64)), [0.25, 0.5, 0.9], atol=2e-4) and r[4] == -1.0
+    # hand value: the median of the profile solves e^-x / 4 + 3 e^(-x/3) / 4 = 1/2 -> x = 1.3966 (Newton in float64)
+    q = 1.0
+    for _ in range(50):
+        q -= (cdf(q) - 0.5) / (np.exp(-q) / 4.0 + np.exp(-q / 3.0) / 4.0)
+    assert abs(r[2] - q) < 2e-3
+
+
+@pytest.mark.parametrize("g", [0.0, 0.005, 0.3, -0.6, 0.9])
+def test_henyey_greenstein_normalised_and_invertible(g):
+    """medium/util.rs:1-19.  henyey_greenstein(g, cos) uses denom = 1 + g^2 + 2 g cos (cos against wo = -ray direction, the PBRT
+    convention) and integrates to 1 over the sphere.  henyey_greenstein_cdf_inverse inverts the CDF of the OTHER sign convention
+    (1 + g^2 - 2 g cos): 1 + g^2 - 2 g cos = ((1 - g^2) / (1 - g + 2 g u))^2 exactly, so the sampled cosine has mean +g while the
+    phase function it is paired with in Homogeneous::sample_wi (homogeneous.rs:62-71) has mean cosine -g — the sampled lobe is the
+    mirror image of the evaluated one for g != 0 (quirk Q25; reproduced, C4 uses g = 0).  Both facts are pinned here."""
+    n = 200001
+    c = np.linspace(-1, 1, n).astype(np.float32)
+    p, _ = orc.hg(g, c)
+    g64 = float(np.float32(g))
+    want = (1 - g64 * g64) / (4 * math.pi * (1 + g64 * g64 + 2 * g64 * c.astype(np.float64)) ** 1.5)
+    assert np.allclose(p, want, rtol=2e-5)
+    integral = 2 * math.pi * np.trapezoid(p.astype(np.float64), c.astype(np.float64))
+    assert abs(integral - 1.0) < 2e-4
+    u = (np.arange(4096) + 0.5) / 4096
+    _, cs = orc.hg(g, u.astype(np.float32))
+    assert cs.min() >= -1.0001 and cs.max() <= 1.0001
+    if abs(g) < 0.01:
+        assert np.allclose(cs, 1 - 2 * u, atol=1e-6)       # isotropic branch (util.rs:11-12)
+    else:
+        # the sampled cosine inverts F(c) = (1 - g^2) / (2 g) * (1 / sqrt(1 + g^2 - 2 g c) - 1 / (1 + g)), the CDF of the MINUS convention
+        c64 = cs.astype(np.float64)
+        cdf = (1 - g64 * g64) / (2 * g64) * (1 / np.sqrt(1 + g64 * g64 - 2 * g64 * c64) - 1 / (1 + g64))
+        assert np.allclose(cdf, u, atol=3e-4)
+        assert abs(c64.mean() - g64) < 2e-3                                                     # mean sampled cosine = +g
+        mean_phase_cos = 2 * math.pi * np.trapezoid(p.astype(np.float64) * c.astype(np.float64), c.astype(np.float64))
+        assert abs(mean_phase_cos - (-g64)) < 2e-3                                              # mean cosine of the evaluated phase = -g
