@@ -25,7 +25,7 @@ CONVERGED = {  # name -> (width, height, spp)
     "c2": (32, 18, 4096),
     "c3": (32, 18, 4096),
     "c4": (32, 18, 4096),
-    "c5": (32, 18, 1024),
+    "c5": (32, 18, 2048),
 }
 REF_THREADS = 18  # fixed, so that the per-thread streams of the faithful mode (and with them the test) do not depend on the host's core count
 

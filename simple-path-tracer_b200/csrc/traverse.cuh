@@ -56,13 +56,15 @@ struct TravCounters { // only maintained by the COUNT instantiations
 #define SPT_INST_UNIFORM_SETUP 1 // 1: the object-space ray setup of an instance visit runs for small meshes too (no divergent branch)
 #endif
 #ifndef SPT_FETCH_MIN_IDLE
-#define SPT_FETCH_MIN_IDLE 3 // refill the warp once this many lanes are without a ray (6 before the pop stage moved to the end of the round)
+#define SPT_FETCH_MIN_IDLE 6 // refill the warp once this many lanes are without a ray (1 / 3 re-measured with the pop stage at the end of the round: -0.5 % / 0 %)
 #endif
 #ifndef SPT_POP_END
 #define SPT_POP_END 1        // 1: the pop stage closes the round instead of opening it (see trace_persistent)
 #endif
 #ifndef SPT_TRI_HELP
-#define SPT_TRI_HELP 1       // 1: ONE triangle pass per round in which lanes without triangle work test the second pending triangle of lanes that have two
+#define SPT_TRI_HELP 0       // 1: ONE triangle pass per round in which lanes without triangle work test the second pending triangle of lanes that have
+                             // two.  Measured on B200 (profiles/README.md, round 2): -10 % on C2 against two plain triangle stages — the pairing
+                             // (3 ballots, a shared-memory map, 11 shuffles, 72 instead of 64 registers) costs more than the lanes it fills return.
 #endif
 
 SPT_D uint32_t sext_s8x4(uint32_t x) { uint32_t v; asm("prmt.b32 %0, %1, 0x0, 0x0000BA98;" : "=r"(v) : "r"(x)); return v; }
@@ -402,10 +404,9 @@ SPT_D bool traverse(const DScene& sc, float3 ow, float3 dw, float tmin, HitRec& 
 // The pop stage CLOSES the round (SPT_POP_END): a ray whose last test ran in this round finds its stack empty now and gives its
 // lane back for the next round's refill; opening the round with it (round 1) cost every ray one whole round at the end of its life
 // in which its lane did nothing else (tools/trav_sim.py: 4.6 -> 3.6 lane-rounds per ray on C2).
-// Triangle pass (SPT_TRI_HELP): every lane with pending triangles tests its next one; lanes that have NO triangle work in this round
-// (a third to two thirds of the warp) each take the second pending triangle of the i-th lane that has two or more — the ray goes over
-// by shuffles, the result comes back the same way and is applied after the owner's own, i.e. in the order a sequential loop would
-// (same hit on equal-t ties).  One such pass does the work of the two triangle stages it replaces.
+// Triangle pass variant (SPT_TRI_HELP, off: measured slower): every lane with pending triangles tests its next one; lanes that have
+// NO triangle work in this round each take the second pending triangle of the i-th lane that has two or more — the ray goes over by
+// shuffles, the result comes back the same way and is applied after the owner's own, i.e. in the order a sequential loop would.
 // A lane drains its pending primitive group before it takes its next node step (same order as a depth-first loop).
 #ifndef SPT_TRI_PER_ROUND
 #define SPT_TRI_PER_ROUND (SPT_TRI_HELP ? 1 : 2)
