@@ -189,16 +189,17 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    reduce_events = []
+    # N > 1: the library's own NCCL communicator (spt_comm_create; torch.distributed only broadcasts the 128-byte id and provides the
+    # barrier / timing reductions).  spt_render_gather renders this rank's tiles and moves only the owned tiles' integer film to rank 0.
+    comm = core.Comm.from_torch(ctx) if world > 1 else None
+    gather_ms = []
 
     def step(seed, flags=0):
-        st = sc.render_device(fb.data_ptr(), w, h, seed=seed, flags=flags, **kw)
         if world > 1:
-            r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            r0.record()
-            dist.reduce(fb, dst=0, op=dist.ReduceOp.SUM)  # framebuffer gather over NVLink (disjoint tiles: exact)
-            r1.record()
-            reduce_events.append((r0, r1))
+            st = sc.render_gather(comm, fb.data_ptr(), w, h, root=0, seed=seed, flags=flags, **kw)
+            gather_ms.append(1e3 * st["seconds_stage"][5])
+        else:
+            st = sc.render_device(fb.data_ptr(), w, h, seed=seed, flags=flags, **kw)
         return st
 
     for i in range(W):
@@ -208,7 +209,7 @@ def main():
     if sampler:
         sampler.start()
     barrier()
-    reduce_events.clear()
+    gather_ms.clear()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     ev0.record()  # spt_render_device returns after its own stream has drained, so events on this stream bracket the device work
@@ -220,7 +221,7 @@ def main():
     # per-rank breakdown of the timed region: device time inside spt_render_device (CUDA events on the library's stream)
     # and of the NCCL framebuffer reduce
     render_ms = 1e3 * sum(s_["seconds_total"] for s_ in stats) / args.steps
-    reduce_ms = sum(a.elapsed_time(b) for a, b in reduce_events) / args.steps if reduce_events else 0.0
+    reduce_ms = sum(gather_ms) / args.steps if gather_ms else 0.0
     brk = torch.tensor([render_ms, reduce_ms, 1e3 * wall / args.steps], dtype=torch.float64, device=dev)
     brk_all = [torch.zeros_like(brk) for _ in range(world)]
     if world > 1:
@@ -325,14 +326,15 @@ def main():
         "config": {"workload": f"{args.workload}: {w}x{h} @ {spp} spp, max_depth 8, recurrence sampler, box r=0.5",
                    "scene": "bunny_5k x3 (conductor, pbr_metallic iso+aniso) + room + emissive quad, power_is MIS" if args.workload == "c2" else args.workload,
                    "parallelism": f"tiles{world}", "pool_slots": pool_slots, "pool_slots_allocated": pool_alloc,
-                   "l2_policy": "per-step working set (path pool %d MB + film %d MB) exceeds the 126 MB L2; no explicit flush" % (pool_alloc * 176 >> 20, w * h * 24 >> 20)},
+                   "l2_policy": "per-step working set (path pool %d MB + film %d MB) exceeds the 126 MB L2; no explicit flush" % (pool_alloc * 180 >> 20, w * h * 24 >> 20)},
         "mrays_per_s": mrays, "rays_per_path": (ext + shadow + probe) / paths,
         "shadow_rays_culled_per_path": sum(s["shadow_culled"] for s in stats) / max(1.0, sum(s["paths"] for s in stats)),
         "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(w * h * 3 * 4)},
         "gpu_launches": int(launches), "roofline": roofline, "clocks": sampler.summary() if sampler else None,
         "timing": {"source": "CUDA events bracketing the K steps, max over ranks", "wall_ms_per_step": float(max(b[2] for b in brk_list)),
                    "render_device_ms_per_rank": [round(float(b[0]), 3) for b in brk_list],
-                   "reduce_ms_per_rank": [round(float(b[1]), 3) for b in brk_list]},
+                   "gather_ms_per_rank": [round(float(b[1]), 3) for b in brk_list],
+                   "gather": "spt_render_gather: owned tiles only, int64 film, grouped ncclSend/ncclRecv to rank 0 + unpack + resolve (device time per rank)"},
     }
     if world == 1 and not args.no_cpu_baseline:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))

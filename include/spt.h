@@ -246,7 +246,7 @@ typedef struct SptRenderDesc { /* OutputConfig (renderer/mod.rs:9-14) + PathTrac
   uint64_t seed;           /* RNG key; the stream of a path depends only on (seed, pixel, sample) */
   int32_t tile_w, tile_h;  /* screen tile size for rank interleaving (0 = SPT_DEFAULT_TILE_W x _H); multiples of 8 / 4 */
   int32_t rank, world_size;/* this process renders the tiles it owns; others stay 0 */
-  int32_t pool_size;       /* resident path slots, 176 B each (0 = default: 1/16 of this rank's camera samples, kept within [2^22, 2^24];
+  int32_t pool_size;       /* resident path slots, 180 B each (0 = default: 1/16 of this rank's camera samples, kept within [2^22, 2^24];
                               fewer for renders of less than 2^22 samples, halved if the device is short of memory) */
   uint32_t flags;
   int32_t spp_first, spp_count; /* render only the samples [spp_first, spp_first + spp_count) of every pixel's spp (0, 0 = all).
@@ -287,7 +287,7 @@ typedef struct SptScene SptScene;
 const char* spt_last_error(void);
 int32_t spt_version(void);
 
-/* One context = one CUDA device (one process per GPU; ranks are joined by the host with NCCL). */
+/* One context = one CUDA device (one process per GPU; ranks are joined with spt_comm_create below). */
 int32_t spt_context_create(int32_t device_id, SptContext** out);
 int32_t spt_context_destroy(SptContext* ctx);
 
@@ -325,6 +325,26 @@ int32_t spt_render(SptScene* scene, const SptRenderDesc* desc, float* out_rgb_me
 /* Same, result left in device memory (width*height*3 f32; pixels of other ranks are 0) so the
  * host can reduce it over NCCL without a round trip. */
 int32_t spt_render_device(SptScene* scene, const SptRenderDesc* desc, float* d_rgb_mean, SptStats* stats);
+
+/* ---- multi-GPU (one process per GPU) ---------------------------------------------------------------------------------------------
+ * The rank join and the framebuffer exchange live behind this ABI, so a host binds ONE library: rank 0 calls spt_comm_unique_id and
+ * hands the SPT_COMM_ID_BYTES bytes to the other ranks by whatever means it has (a file, a socket, MPI, a torch.distributed
+ * broadcast), every rank calls spt_comm_create (ncclCommInitRank on its context's device; collective: all ranks must call it), and
+ * then spt_render_gather per frame.  NCCL is loaded at run time (dlopen of libnccl.so.2); without it these calls return
+ * SPT_ERR_UNSUPPORTED and everything else works.  The reference has no counterpart: it threads row bands in one process
+ * (renderer/pt.rs:243-261). */
+#define SPT_COMM_ID_BYTES 128
+typedef struct SptComm SptComm;
+int32_t spt_comm_unique_id(uint8_t* out_id /* SPT_COMM_ID_BYTES */);
+int32_t spt_comm_create(SptContext* ctx, const uint8_t* id /* SPT_COMM_ID_BYTES */, int32_t rank, int32_t world_size, SptComm** out);
+int32_t spt_comm_destroy(SptComm* comm);
+/* ≙ RendererT::render over all ranks of `comm`: every rank renders the interleaved tiles it owns (desc->rank / world_size are taken
+ * from the communicator), then ONLY the owned tiles travel — as the integer film, 3 x int64 per pixel, by grouped ncclSend/ncclRecv
+ * over NVLink — to `root`, which unpacks them into its film and reconstructs the frame into d_rgb_mean (DEVICE memory,
+ * width*height*3 f32; ignored on the other ranks, may be NULL there).  Because the film is integer the result is bit-identical to the
+ * one-GPU frame for every filter radius.  stats (may be NULL) are this rank's; seconds_stage[5] = device time of exchange + resolve.
+ * Collective: every rank must call it with the same desc. */
+int32_t spt_render_gather(SptScene* scene, SptComm* comm, const SptRenderDesc* desc, int32_t root, float* d_rgb_mean, SptStats* stats);
 
 /* Progressive dump / resume: the film is 3 x int64 per pixel (sums in 2^-24 fixed point), row 0 = top.  spt_film_save copies the
  * film of the last render on this scene to the host (n_values = width*height*3); spt_film_load installs one as if `spp_done`

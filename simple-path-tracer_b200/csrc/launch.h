@@ -36,6 +36,8 @@ void launch_shade(int mat, const DScene& sc, const RenderParams& P, bool count, 
 void launch_generate(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st);
 void launch_resolve(const long long* film, int n_pixels, float inv_spp, float* out_mean, uint8_t* out_rgb8, int grid, cudaStream_t st);
 void launch_resolve_box(const RenderParams& P, int k0, int n_k, float radius, int radius_int, float* out_mean, uint8_t* out_rgb8, int grid, cudaStream_t st);
+void launch_pack_tiles(const long long* film, const uint32_t* tiles, int n_tiles, const RenderParams& P, long long* out, int grid, cudaStream_t st);
+void launch_unpack_tiles(long long* film, const uint32_t* all_tiles, int per_rank, int world, int root, const RenderParams& P, const long long* in, int grid, cudaStream_t st);
 void launch_aov_normal(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st);
 void launch_bxdf(const DScene& sc, const SptBxdfQuery* q, long long n, SptBxdfResult* out, int grid, cudaStream_t st);
 // defined per shade translation unit

@@ -10,7 +10,10 @@
 __global__ void __launch_bounds__(SPT_LOGIC_BLOCK) k_logic(const DScene sc, const RenderParams P) {
   __shared__ uint32_t s_cnt[SPT_NQ], s_base[SPT_NQ];
   if (threadIdx.x < SPT_NQ) s_cnt[threadIdx.x] = 0;
-  if (blockIdx.x == 0 && threadIdx.x == 0) { P.ctr->it.live = 0; P.ctr->it.next_ext = 0; P.ctr->it.sq = 0; P.ctr->it.next_con = 0; } // connect + extend of the last iteration are done
+  if (blockIdx.x == 0 && threadIdx.x == 0) { // connect + extend of the last iteration are done
+    P.ctr->it.live = 0; P.ctr->it.next_ext = 0; P.ctr->it.sq = 0; P.ctr->it.next_con = 0; P.ctr->it.n_ext = 0;
+    P.ctr->it.drain = (P.use_ext_queue && P.ctr->cursor >= P.total_samples) ? 1u : 0u; // the cursor only moves in generate: one value for the whole iteration
+  }
   __syncthreads();
   const int slot = blockIdx.x * blockDim.x + threadIdx.x;
   int cls = -1; uint32_t rank = 0;
@@ -125,6 +128,28 @@ __global__ void __launch_bounds__(SPT_LOGIC_BLOCK) k_generate(const DScene sc, c
   if (blockIdx.x == 0 && threadIdx.x < SPT_NQ) P.ctr->it.q[threadIdx.x] = 0; // the shade kernels of this iteration are done
   uint32_t n_new = 0, n_live = 0;
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  if (P.ctr->it.drain) {
+    // Every camera sample has been started: nothing to regenerate.  The pool now empties within max_depth iterations, and a kernel
+    // that scans it finds fewer and fewer rays per chunk (at 10 % live a lane of k_extend spends 9 rounds finding a ray that lives 4).
+    // So this pass compacts the live slots into ext_queue (one atomic per block and trip) and k_extend fetches from that list.
+    for (int base_slot = blockIdx.x * blockDim.x; base_slot < P.pool.n; base_slot += gridDim.x * blockDim.x) {
+      const int slot = base_slot + (int)threadIdx.x;
+      const bool live = slot < P.pool.n && (P.pool.flags[slot] & 1u);
+      const uint32_t m = __ballot_sync(0xffffffffu, live);
+      if (lane == 0) s_warp[warp] = __popc(m);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        uint32_t total = 0;
+        for (int w = 0; w < SPT_LOGIC_BLOCK / 32; w++) { const uint32_t c = s_warp[w]; s_warp[w] = total; total += c; }
+        s_base = total ? (unsigned long long)atomicAdd(&P.ctr->it.n_ext, total) : 0ull;
+      }
+      __syncthreads();
+      if (live) { P.ext_queue[(uint32_t)s_base + s_warp[warp] + __popc(m & ((1u << lane) - 1u))] = (uint32_t)slot; n_live++; }
+      __syncthreads();
+    }
+    warp_sum_to32(&P.ctr->it.live, n_live);
+    return;
+  }
   for (int base_slot = blockIdx.x * blockDim.x; base_slot < P.pool.n; base_slot += gridDim.x * blockDim.x) {
     const int slot = base_slot + (int)threadIdx.x;
     const bool in_range = slot < P.pool.n;
@@ -211,12 +236,39 @@ __global__ void k_resolve_box(const RenderParams P, int k0, int n_k, float radiu
   }
 }
 
+// ---- tile-packed film exchange (spt_render_gather): 3 x int64 per pixel of the tiles a rank owns, tile-major ---------------------------------
+__global__ void k_pack_tiles(const long long* __restrict__ film, const uint32_t* __restrict__ tiles, int n_tiles, const RenderParams P, long long* __restrict__ out) {
+  const int tp = P.tile_w * P.tile_h;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < (long long)n_tiles * tp; i += (long long)gridDim.x * blockDim.x) {
+    const int t = (int)(i / tp), q = (int)(i % tp);
+    const uint32_t tile = tiles[t];
+    const int x = (int)(tile % (uint32_t)P.tiles_x) * P.tile_w + q % P.tile_w, y = (int)(tile / (uint32_t)P.tiles_x) * P.tile_h + q / P.tile_w;
+    long long v[3] = {0, 0, 0};
+    if (x < P.width && y < P.height) { const size_t px = (size_t)y * P.width + x; v[0] = film[3 * px]; v[1] = film[3 * px + 1]; v[2] = film[3 * px + 2]; }
+    out[3 * i] = v[0]; out[3 * i + 1] = v[1]; out[3 * i + 2] = v[2];
+  }
+}
+// root: segment r of `in` holds rank r's tiles in the order of all_tiles[r * per_rank ..] (0xffffffff = padding); the root's own segment is skipped
+__global__ void k_unpack_tiles(long long* __restrict__ film, const uint32_t* __restrict__ all_tiles, int per_rank, int world, int root, const RenderParams P,
+                               const long long* __restrict__ in) {
+  const int tp = P.tile_w * P.tile_h;
+  const long long n = (long long)world * per_rank * tp;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const long long t = i / tp; const int q = (int)(i % tp);
+    if ((int)(t / per_rank) == root) continue;
+    const uint32_t tile = all_tiles[t];
+    if (tile == 0xffffffffu) continue;
+    const int x = (int)(tile % (uint32_t)P.tiles_x) * P.tile_w + q % P.tile_w, y = (int)(tile / (uint32_t)P.tiles_x) * P.tile_h + q / P.tile_w;
+    if (x < P.width && y < P.height) { const size_t px = (size_t)y * P.width + x; film[3 * px] = in[3 * i]; film[3 * px + 1] = in[3 * i + 1]; film[3 * px + 2] = in[3 * i + 2]; }
+  }
+}
+
 // ---- debug_normal AOV (the reference's cargo feature `debug_normal`, pt.rs:113-118) ---------------------------------------------------
 // Takes the place of logic + special + shade in the wavefront loop: every live path is a camera ray that k_extend has just traced.
 // First surface hit -> colour = 0.5 * inter.normal + 0.5 (the interpolated, instance-transformed normal of Triangle::intersect /
 // Sphere::intersect, not the normal-mapped shading frame); miss -> the environment as at depth 0 (pt.rs:97-111); path ends.
 __global__ void __launch_bounds__(SPT_LOGIC_BLOCK) k_aov_normal(const DScene sc, const RenderParams P) {
-  if (blockIdx.x == 0 && threadIdx.x == 0) { P.ctr->it.live = 0; P.ctr->it.next_ext = 0; P.ctr->it.sq = 0; P.ctr->it.next_con = 0; }
+  if (blockIdx.x == 0 && threadIdx.x == 0) { P.ctr->it.live = 0; P.ctr->it.next_ext = 0; P.ctr->it.sq = 0; P.ctr->it.next_con = 0; P.ctr->it.n_ext = 0; P.ctr->it.drain = 0; }
   uint32_t nonfinite = 0;
   for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < P.pool.n; slot += gridDim.x * blockDim.x) {
     const uint32_t flags = P.pool.flags[slot];
@@ -269,6 +321,12 @@ void launch_resolve(const long long* film, int n_pixels, float inv_spp, float* o
 }
 void launch_resolve_box(const RenderParams& P, int k0, int n_k, float radius, int radius_int, float* out_mean, uint8_t* out_rgb8, int grid, cudaStream_t st) {
   k_resolve_box<<<grid, 128, 0, st>>>(P, k0, n_k, radius, radius_int, out_mean, out_rgb8);
+}
+void launch_pack_tiles(const long long* film, const uint32_t* tiles, int n_tiles, const RenderParams& P, long long* out, int grid, cudaStream_t st) {
+  k_pack_tiles<<<grid, 128, 0, st>>>(film, tiles, n_tiles, P, out);
+}
+void launch_unpack_tiles(long long* film, const uint32_t* all_tiles, int per_rank, int world, int root, const RenderParams& P, const long long* in, int grid, cudaStream_t st) {
+  k_unpack_tiles<<<grid, 128, 0, st>>>(film, all_tiles, per_rank, world, root, P, in);
 }
 void launch_aov_normal(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st) { k_aov_normal<<<grid, SPT_LOGIC_BLOCK, 0, st>>>(sc, P); }
 void launch_bxdf(const DScene& sc, const SptBxdfQuery* q, long long n, SptBxdfResult* out, int grid, cudaStream_t st) {

@@ -52,6 +52,9 @@ struct SptScene {
   void* stage_rays = nullptr; void* stage_out = nullptr; size_t stage_rays_bytes = 0, stage_out_bytes = 0; // device staging of the host-buffer entry points (grown on demand, kept)
   uint32_t* tiles = nullptr; size_t tiles_cap = 0, n_tiles = 0; int tile_key[6] = {0, 0, 0, 0, 0, 0};
   float* out_mean = nullptr; uint8_t* out_rgb8 = nullptr; size_t out_px = 0;
+  RenderParams last_P{};                             // parameters of the last render (what the film holds): the resolve of spt_render_gather needs them
+  long long* gather_buf = nullptr; size_t gather_bytes = 0;   // spt_render_gather: tile-packed film of this rank (root: of every rank)
+  uint32_t* all_tiles = nullptr; size_t all_tiles_cap = 0; int all_tiles_key[6] = {0, 0, 0, 0, 0, 0}; // root: every rank's tile list, rank-major, padded to the same length
   DevCounters* h_ctr = nullptr; // pinned
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[2] = {nullptr, nullptr};
@@ -227,7 +230,7 @@ int32_t spt_scene_destroy(SptScene* s) {
   for (DevBuf& b : s->bufs) { if (!b.in_arena) cudaFree(b.d); if (b.h) cudaFreeHost(b.h); }
   cudaFree(s->hot_arena);
   cudaFree(s->pool_mem); cudaFree(s->film); cudaFree(s->ctr); cudaFree(s->batch_next); cudaFree(s->tiles);
-  cudaFree(s->out_mean); cudaFree(s->out_rgb8); cudaFree(s->stage_rays); cudaFree(s->stage_out);
+  cudaFree(s->out_mean); cudaFree(s->out_rgb8); cudaFree(s->stage_rays); cudaFree(s->stage_out); cudaFree(s->gather_buf); cudaFree(s->all_tiles);
   if (s->h_ctr) cudaFreeHost(s->h_ctr);
   if (s->ev[0]) cudaEventDestroy(s->ev[0]);
   if (s->ev[1]) cudaEventDestroy(s->ev[1]);
@@ -342,8 +345,19 @@ std::vector<uint32_t> owned_tiles(int width, int height, int tw, int th, int ran
   return mine;
 }
 
+// Film::filter_to_image on the device: the film of the last render -> mean image (+ 8-bit encode)
+void resolve_film(SptScene* s, float radius, float* d_mean, uint8_t* d_rgb8, cudaStream_t st) {
+  const RenderParams& P = s->last_P;
+  const size_t n_px = (size_t)P.width * P.height;
+  if (radius == 0.5f) // own-pixel mean (Q14: radius_int = 0 and every sample of the pixel lies in the box)
+    spt::launch_resolve(s->film, (int)n_px, 1.0f / (float)s->film_spp, d_mean, d_rgb8, grid_for(s->ctx, (long long)n_px * 3, 8), st);
+  else
+    spt::launch_resolve_box(P, s->film_k0, s->film_spp, radius, (int)std::ceil(radius - 0.5f), d_mean, d_rgb8, grid_for(s->ctx, (long long)n_px, 16), st);
+}
+
+// d_mean == nullptr: leave the film unresolved (spt_render_gather resolves on the root after the exchange)
 int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_rgb8, SptStats* stats) {
-  if (!s || !r || !d_mean) return fail(SPT_ERR_INVALID, "spt_render: null argument");
+  if (!s || !r) return fail(SPT_ERR_INVALID, "spt_render: null argument");
   if (r->width <= 0 || r->height <= 0 || r->max_depth < 0 || r->max_depth > 255) return fail(SPT_ERR_INVALID, "spt_render: bad width/height/max_depth");
   if (r->camera_index < 0 || r->camera_index >= (int)s->cameras.size()) return fail(SPT_ERR_INVALID, "spt_render: bad camera index");
   if (r->sampler_kind < 0 || r->sampler_kind > 2) return fail(SPT_ERR_INVALID, "spt_render: unknown sampler");
@@ -379,7 +393,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   int pool_n = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 24, std::max<unsigned long long>(pool_lo, rank_samples / 8ull)); // allocated
   int pool_start = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 24, std::max<unsigned long long>(pool_lo, rank_samples / 16ull)); // active at first
   pool_n = round_pool(pool_n); pool_start = std::min(pool_n, round_pool(pool_start));
-  const size_t per_slot = sizeof(PathRec) + sizeof(float4) + 3 * sizeof(float4) + sizeof(int32_t) + sizeof(uint32_t) + SPT_NQ * sizeof(uint32_t);
+  const size_t per_slot = sizeof(PathRec) + sizeof(float4) + 3 * sizeof(float4) + sizeof(int32_t) + sizeof(uint32_t) + (SPT_NQ + 1) * sizeof(uint32_t);
   if (s->pool_n != pool_n) {
     cudaFree(s->pool_mem); s->pool_mem = nullptr; s->pool_n = 0;
     // a pool the CALLER asked for must fit; the default one shrinks (down to the 2^22 rule) if the device is short of memory
@@ -403,6 +417,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
     P.pool.hit_inst = (int32_t*)p; p += N * sizeof(int32_t);
     P.pool.flags = (uint32_t*)p; p += N * sizeof(uint32_t);
     P.queue = (uint32_t*)p; p += N * SPT_NQ * sizeof(uint32_t);
+    P.ext_queue = (uint32_t*)p; p += N * sizeof(uint32_t);
     P.pool.n = pool_start; // active slots; the arrays hold pool_n
   }
   P.ctr = s->ctr; P.film = s->film;
@@ -421,6 +436,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   P.sampler = r->sampler_kind; P.spp = spp_pass; P.spp_first = spp_first; P.spp_frame = spp; P.div_x = std::max(1, r->div_x); P.div_y = std::max(1, r->div_y);
   P.seed = r->seed;
   P.sort_materials = (r->flags & SPT_RENDER_NO_SORT) ? 0 : 1;
+  { const char* e = getenv("SPT_EXT_QUEUE"); P.use_ext_queue = (e && atoi(e) == 0) ? 0 : 1; }
   P.total_samples = (unsigned long long)s->n_tiles * (unsigned long long)(tw * th) * (unsigned long long)spp_pass;
   DScene ds = s->ds;
   ds.camera = s->cameras[r->camera_index];
@@ -549,12 +565,8 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
       if (s->h_ctr->it.live == 0 && s->h_ctr->cursor >= P.total_samples) break;
     }
   }
-  if (r->filter_radius == 0.5f) // own-pixel mean (Q14: radius_int = 0 and every sample of the pixel lies in the box)
-    spt::launch_resolve(s->film, (int)n_px, 1.0f / (float)s->film_spp, d_mean, d_rgb8, grid_for(s->ctx, (long long)n_px * 3, 8), st);
-  else
-    spt::launch_resolve_box(P, s->film_k0, s->film_spp, r->filter_radius, (int)std::ceil(r->filter_radius - 0.5f), d_mean, d_rgb8,
-                            grid_for(s->ctx, (long long)n_px, 16), st);
-  launches++;
+  s->last_P = P;
+  if (d_mean) { resolve_film(s, r->filter_radius, d_mean, d_rgb8, st); launches++; }
   CU(cudaEventRecord(s->ev[1], st));
   CU(cudaMemcpyAsync(s->h_ctr, s->ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
@@ -595,7 +607,138 @@ extern "C" int32_t spt_film_load(SptScene* s, const int64_t* values, int32_t wid
 }
 
 extern "C" int32_t spt_render_device(SptScene* s, const SptRenderDesc* r, float* d_rgb_mean, SptStats* stats) {
+  if (!d_rgb_mean) return fail(SPT_ERR_INVALID, "spt_render_device: null output");
   return render_impl(s, r, d_rgb_mean, nullptr, stats);
+}
+
+// ---- multi-GPU: the rank join and the framebuffer exchange behind the C ABI -------------------------------------------------------------
+// NCCL is bound at run time (dlopen of libnccl.so.2: the copy a host such as PyTorch has already loaded, else the system one), so the
+// library has no link-time dependency on it and single-GPU hosts never touch it.
+#include <dlfcn.h>
+#include <nccl.h>
+namespace {
+struct NcclApi {
+  void* lib = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+NcclApi g_nccl;
+int nccl_load() {
+  if (g_nccl.lib) return SPT_OK;
+  void* h = nullptr;
+  for (const char* name : {"libnccl.so.2", "libnccl.so"}) { h = dlopen(name, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
+  if (!h) return fail(SPT_ERR_UNSUPPORTED, std::string("spt_comm: cannot load libnccl.so.2 (") + dlerror() + ")");
+  NcclApi a; a.lib = h;
+  bool ok = true;
+  auto sym = [&](const char* n) { void* p = dlsym(h, n); ok = ok && p; return p; };
+  a.GetUniqueId = (decltype(a.GetUniqueId))sym("ncclGetUniqueId"); a.CommInitRank = (decltype(a.CommInitRank))sym("ncclCommInitRank");
+  a.CommDestroy = (decltype(a.CommDestroy))sym("ncclCommDestroy"); a.Send = (decltype(a.Send))sym("ncclSend"); a.Recv = (decltype(a.Recv))sym("ncclRecv");
+  a.GroupStart = (decltype(a.GroupStart))sym("ncclGroupStart"); a.GroupEnd = (decltype(a.GroupEnd))sym("ncclGroupEnd");
+  a.GetErrorString = (decltype(a.GetErrorString))sym("ncclGetErrorString");
+  if (!ok) return fail(SPT_ERR_UNSUPPORTED, "spt_comm: libnccl.so.2 lacks a required symbol");
+  g_nccl = a;
+  return SPT_OK;
+}
+#define NC(call)                                                                                                   \
+  do {                                                                                                             \
+    ncclResult_t r_ = (call);                                                                                      \
+    if (r_ != ncclSuccess) return fail(SPT_ERR_CUDA, std::string(#call) + ": " + g_nccl.GetErrorString(r_));        \
+  } while (0)
+} // namespace
+
+struct SptComm { SptContext* ctx = nullptr; ncclComm_t comm = nullptr; int rank = 0, world = 1; };
+
+extern "C" int32_t spt_comm_unique_id(uint8_t* out_id) {
+  if (!out_id) return fail(SPT_ERR_INVALID, "spt_comm_unique_id: null argument");
+  static_assert(sizeof(ncclUniqueId) == SPT_COMM_ID_BYTES, "SPT_COMM_ID_BYTES must equal sizeof(ncclUniqueId)");
+  const int st = nccl_load();
+  if (st != SPT_OK) return st;
+  ncclUniqueId id;
+  NC(g_nccl.GetUniqueId(&id));
+  memcpy(out_id, &id, sizeof(id));
+  return SPT_OK;
+}
+
+extern "C" int32_t spt_comm_create(SptContext* ctx, const uint8_t* id, int32_t rank, int32_t world_size, SptComm** out) {
+  if (!ctx || !id || !out || world_size < 1 || rank < 0 || rank >= world_size) return fail(SPT_ERR_INVALID, "spt_comm_create: bad argument");
+  const int st = nccl_load();
+  if (st != SPT_OK) return st;
+  CU(cudaSetDevice(ctx->device));
+  ncclUniqueId nid; memcpy(&nid, id, sizeof(nid));
+  SptComm* c = new (std::nothrow) SptComm();
+  if (!c) return fail(SPT_ERR_INVALID, "out of host memory");
+  c->ctx = ctx; c->rank = rank; c->world = world_size;
+  const ncclResult_t r = g_nccl.CommInitRank(&c->comm, world_size, nid, rank);
+  if (r != ncclSuccess) { delete c; return fail(SPT_ERR_CUDA, std::string("ncclCommInitRank: ") + g_nccl.GetErrorString(r)); }
+  *out = c;
+  return SPT_OK;
+}
+
+extern "C" int32_t spt_comm_destroy(SptComm* c) {
+  if (!c) return SPT_OK;
+  if (c->comm && g_nccl.CommDestroy) { cudaSetDevice(c->ctx->device); g_nccl.CommDestroy(c->comm); }
+  delete c;
+  return SPT_OK;
+}
+
+// Render this rank's tiles, then move ONLY the tiles each rank owns — as the integer film, 3 x int64 per pixel — to `root` with
+// grouped ncclSend / ncclRecv, unpack them into the root's film and reconstruct there.  W*H*24 bytes cross NVLink in total instead of
+// a W*H*12-byte full-frame reduce PER RANK, and because the film is integer the gathered frame is bit-identical to the one-GPU frame
+// for every filter radius (the neighbour sums a radius > 0.5 needs exist on the root after the unpack).
+extern "C" int32_t spt_render_gather(SptScene* s, SptComm* c, const SptRenderDesc* desc, int32_t root, float* d_rgb_mean, SptStats* stats) {
+  if (!s || !c || !desc) return fail(SPT_ERR_INVALID, "spt_render_gather: null argument");
+  if (root < 0 || root >= c->world) return fail(SPT_ERR_INVALID, "spt_render_gather: bad root");
+  if (c->rank == root && !d_rgb_mean) return fail(SPT_ERR_INVALID, "spt_render_gather: the root needs an output buffer");
+  if (s->ctx->device != c->ctx->device) return fail(SPT_ERR_INVALID, "spt_render_gather: scene and communicator live on different devices");
+  SptRenderDesc rd = *desc;
+  rd.rank = c->rank; rd.world_size = c->world;
+  int st = render_impl(s, &rd, nullptr, nullptr, stats);
+  if (st != SPT_OK) return st;
+  cudaStream_t cs = s->stream;
+  const RenderParams& P = s->last_P;
+  const int tw = P.tile_w, th = P.tile_h, tiles_x = P.tiles_x, tiles_y = (P.height + th - 1) / th, n_all = tiles_x * tiles_y;
+  const size_t per_rank_tiles = (size_t)(n_all + c->world - 1) / c->world;            // ranks own n_all / world tiles, +-1
+  const size_t tile_vals = (size_t)tw * th * 3, seg = per_rank_tiles * tile_vals;      // int64 values per rank segment
+  const bool is_root = c->rank == root;
+  const size_t need = (is_root ? (size_t)c->world : 1) * seg * sizeof(long long);
+  if (s->gather_bytes < need) { cudaFree(s->gather_buf); s->gather_buf = nullptr; s->gather_bytes = 0; CU(cudaMalloc(&s->gather_buf, need)); s->gather_bytes = need; }
+  CU(cudaEventRecord(s->sev[0], cs));
+  const int key[6] = {P.width, P.height, tw, th, root, c->world};
+  if (is_root && c->world > 1 && (!s->all_tiles || memcmp(key, s->all_tiles_key, sizeof(key)) != 0)) { // every rank's tile list, rank-major
+    std::vector<uint32_t> all((size_t)c->world * per_rank_tiles, 0xffffffffu);
+    for (int r = 0; r < c->world; r++) {
+      const std::vector<uint32_t> t = owned_tiles(P.width, P.height, tw, th, r, c->world);
+      std::copy(t.begin(), t.end(), all.begin() + (size_t)r * per_rank_tiles);
+    }
+    if (s->all_tiles_cap < all.size()) { cudaFree(s->all_tiles); s->all_tiles = nullptr; CU(cudaMalloc(&s->all_tiles, all.size() * sizeof(uint32_t))); s->all_tiles_cap = all.size(); }
+    CU(cudaMemcpyAsync(s->all_tiles, all.data(), all.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, cs));
+    CU(cudaStreamSynchronize(cs)); // `all` goes out of scope
+    memcpy(s->all_tiles_key, key, sizeof(key));
+  }
+  if (c->world > 1) {
+    if (!is_root) spt::launch_pack_tiles(s->film, s->tiles, (int)s->n_tiles, P, s->gather_buf, grid_for(s->ctx, (long long)s->n_tiles * tw * th, 8), cs);
+    CU(cudaGetLastError());
+    NC(g_nccl.GroupStart());
+    if (is_root) { for (int r = 0; r < c->world; r++) if (r != root) NC(g_nccl.Recv(s->gather_buf + (size_t)r * seg, seg, ncclInt64, r, c->comm, cs)); }
+    else NC(g_nccl.Send(s->gather_buf, seg, ncclInt64, root, c->comm, cs));
+    NC(g_nccl.GroupEnd());
+    if (is_root) { // the other ranks' tiles into the root's film (its own are there already)
+      spt::launch_unpack_tiles(s->film, s->all_tiles, (int)per_rank_tiles, c->world, root, P, s->gather_buf, grid_for(s->ctx, (long long)c->world * per_rank_tiles * tw * th, 8), cs);
+      CU(cudaGetLastError());
+    }
+  }
+  if (is_root) resolve_film(s, rd.filter_radius, d_rgb_mean, nullptr, cs);
+  CU(cudaEventRecord(s->sev[1], cs));
+  CU(cudaStreamSynchronize(cs));
+  CU(cudaGetLastError());
+  if (stats) { float ms = 0.f; cudaEventElapsedTime(&ms, s->sev[0], s->sev[1]); stats->seconds_stage[5] = ms * 1e-3; stats->kernel_launches += is_root ? 2 : 1; }
+  return SPT_OK;
 }
 
 extern "C" int32_t spt_render(SptScene* s, const SptRenderDesc* r, float* out_rgb_mean, uint8_t* out_rgb8, SptStats* stats) {

@@ -15,18 +15,22 @@ SPT_D void flush_trav_counters(DevCounters* ctr, const TravCounters& tc) {
 struct ExtendSrc { // every live path of the pool: closest hit (pt.rs:49-50)
   const RenderParams& P;
   uint32_t n_rays;
+  uint32_t n_list; // 0: scan the pool slots; > 0 (draining pool): the live slots are listed in P.ext_queue[0 .. n_list)
   static constexpr uint32_t kChunk = SPT_EXTEND_CHUNK;
-  SPT_D uint32_t total() const { return (uint32_t)P.pool.n; }
+  SPT_D uint32_t total() const { return n_list ? n_list : (uint32_t)P.pool.n; }
+  SPT_D uint32_t slot_of(uint32_t i) const { return n_list ? P.ext_queue[i] : i; }
   SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
-    if (!(P.pool.flags[i] & 1u)) return false;
-    const float4 o4 = P.pool.rec[i].ray_o, d4 = P.pool.rec[i].ray_d;
+    const uint32_t s = slot_of(i);
+    if (!(P.pool.flags[s] & 1u)) return false;
+    const float4 o4 = P.pool.rec[s].ray_o, d4 = P.pool.rec[s].ray_d;
     o = mk3(o4); d = mk3(d4); tmin = o4.w; tmax = FLT_MAX; // Intersection::default, intersection.rs:86-102
     n_rays++;
     return true;
   }
   SPT_D void store(uint32_t i, const HitRec& h) {
-    P.pool.hit[i] = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
-    P.pool.hit_inst[i] = h.inst;
+    const uint32_t s = slot_of(i);
+    P.pool.hit[s] = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
+    P.pool.hit_inst[s] = h.inst;
   }
 };
 struct ConnectSrc { // the queued shadow rays: any hit (pt.rs:81, :169); unoccluded contributions go to the film
@@ -55,7 +59,8 @@ struct ConnectSrc { // the queued shadow rays: any hit (pt.rs:81, :169); unocclu
 template <bool COUNT>
 __global__ void SPT_TRAV_BOUNDS k_extend(const DScene sc, const RenderParams P) {
   TravCounters tc = {};
-  ExtendSrc src{P, 0};
+  ExtendSrc src{P, 0, P.ctr->it.drain ? P.ctr->it.n_ext : 0u};
+  if (P.ctr->it.drain && src.n_list == 0u) return; // a draining pool without a live path
   trace_persistent<false, COUNT>(sc, src, &P.ctr->it.next_ext, tc);
   warp_sum_to(&P.ctr->ext_rays, src.n_rays);
   if (COUNT) flush_trav_counters(P.ctr, tc);

@@ -29,7 +29,9 @@ struct IterCounters { // per-iteration device counters; each is zeroed by a kern
   uint32_t live;        // live slots after generate (read by the host; zeroed by logic)
   uint32_t next_ext;    // ray-fetch cursor of extend  (zeroed by logic)
   uint32_t next_con;    // ray-fetch cursor of connect (zeroed by logic)
-  uint32_t pad[2];
+  uint32_t drain;       // 1: every camera sample has been started (set by logic): generate compacts the live slots into ext_queue and extend
+                        //    fetches from that list instead of scanning a mostly empty pool
+  uint32_t n_ext;       // entries of ext_queue (producer: generate in drain mode, consumer: extend; zeroed by logic)
 };
 struct DevCounters { // device-side totals of one render
   unsigned long long cursor;      // next camera-sample ordinal
@@ -41,6 +43,7 @@ struct RenderParams {
   PathPool pool;
   ShadowQueue sq;
   uint32_t* queue;   // SPT_NQ arrays of pool.n slot ids
+  uint32_t* ext_queue; // pool.n slot ids: the live slots of a draining pool (see IterCounters::drain)
   DevCounters* ctr;
   long long* film; // 3 per pixel
   const uint32_t* tiles; // owned tile ids
@@ -49,6 +52,7 @@ struct RenderParams {
   int32_t sampler, spp, div_x, div_y; // spp = samples per pixel rendered by THIS call
   int32_t spp_first, spp_frame;       // index of its first sample; samples per pixel of the whole frame (sampler ordinals)
   int32_t sort_materials; // 0: every surface hit goes to the generic queue (SPT_RENDER_NO_SORT)
+  int32_t use_ext_queue;  // 1: a draining pool is compacted for extend (IterCounters::drain); SPT_EXT_QUEUE=0 turns it off for A/B timing
   uint64_t seed;
   unsigned long long total_samples; // n_tiles * tile_w * tile_h * spp
 };

@@ -139,7 +139,9 @@ class SceneInfo(C.Structure):
 SYMBOLS = ["spt_last_error", "spt_version", "spt_context_create", "spt_context_destroy", "spt_scene_create",
            "spt_scene_upload", "spt_scene_info", "spt_scene_destroy", "spt_trace_batch", "spt_occluded_batch",
            "spt_trace_batch_device", "spt_occluded_batch_device", "spt_bxdf_batch", "spt_render",
-           "spt_render_device", "spt_film_save", "spt_film_load", "spt_owned_tiles"]
+           "spt_render_device", "spt_film_save", "spt_film_load", "spt_owned_tiles",
+           "spt_comm_unique_id", "spt_comm_create", "spt_comm_destroy", "spt_render_gather"]
+COMM_ID_BYTES = 128
 
 PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_PATH = os.path.join(PKG_ROOT, "lib", "libspt_cuda.so")
@@ -180,6 +182,10 @@ def load_library(path=None):
         "spt_film_save": [vp, vp, C.c_int64],
         "spt_film_load": [vp, vp, C.c_int32, C.c_int32, C.c_int32],
         "spt_owned_tiles": [C.c_int32] * 6 + [vp, C.c_int64, P(C.c_int64)],
+        "spt_comm_unique_id": [vp],
+        "spt_comm_create": [vp, vp, C.c_int32, C.c_int32, P(vp)],
+        "spt_comm_destroy": [vp],
+        "spt_render_gather": [vp, vp, P(RenderDesc), C.c_int32, vp, P(Stats)],
     }
     for name, args in sig.items():
         fn = getattr(lib, name)

@@ -23,6 +23,42 @@ class Context:
             self.h = C.c_void_p()
 
 
+class Comm:
+    """spt_comm_create: this process' rank in the library's NCCL communicator (one process per GPU).  `id_bytes`: the 128 bytes rank 0
+    got from Comm.unique_id(), handed to every rank by the host (see Comm.from_torch)."""
+
+    def __init__(self, ctx, id_bytes, rank, world_size):
+        self.ctx, self.lib, self.rank, self.world_size = ctx, ctx.lib, rank, world_size
+        buf = (C.c_uint8 * abi.COMM_ID_BYTES).from_buffer_copy(bytes(id_bytes))
+        self.h = C.c_void_p()
+        abi.check(self.lib, self.lib.spt_comm_create(ctx.h, buf, rank, world_size, C.byref(self.h)))
+
+    @staticmethod
+    def unique_id(lib=None):
+        lib = lib or abi.load_library()
+        buf = (C.c_uint8 * abi.COMM_ID_BYTES)()
+        abi.check(lib, lib.spt_comm_unique_id(buf))
+        return bytes(buf)
+
+    @classmethod
+    def from_torch(cls, ctx):
+        """Join the ranks of an initialised torch.distributed process group: rank 0 creates the id, a broadcast hands it round."""
+        import torch
+        import torch.distributed as dist
+        rank, world = dist.get_rank(), dist.get_world_size()
+        dev = torch.device("cuda", ctx.device) if dist.get_backend() == "nccl" else torch.device("cpu")
+        t = torch.zeros(abi.COMM_ID_BYTES, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            t.copy_(torch.frombuffer(bytearray(cls.unique_id(ctx.lib)), dtype=torch.uint8))
+        dist.broadcast(t, src=0)
+        return cls(ctx, bytes(t.cpu().numpy().tobytes()), rank, world)
+
+    def close(self):
+        if self.h:
+            self.lib.spt_comm_destroy(self.h)
+            self.h = C.c_void_p()
+
+
 class Scene:
     """spt_scene_create on a FlatScene (spt.loader)."""
 
@@ -118,6 +154,15 @@ class Scene:
         """spt_film_load: resume from a saved film that holds spp_done samples per pixel."""
         film = np.ascontiguousarray(film, np.int64)
         abi.check(self.lib, self.lib.spt_film_load(self.h, film.ctypes.data, film.shape[1], film.shape[0], spp_done))
+
+    def render_gather(self, comm, d_out_ptr, width, height, root=0, **kw):
+        """spt_render_gather: every rank of `comm` renders its tiles; the root receives the tile-packed film of the others over NCCL and
+        leaves the full frame at d_out_ptr (device memory, width*height*3 f32; ignored on the other ranks).  Returns this rank's stats."""
+        kw.pop("rank", None); kw.pop("world_size", None)
+        rd = self.render_desc(width, height, rank=comm.rank, world_size=comm.world_size, **kw)
+        st = abi.Stats()
+        abi.check(self.lib, self.lib.spt_render_gather(self.h, comm.h, C.byref(rd), root, d_out_ptr, C.byref(st)))
+        return st.as_dict()
 
     def render_device(self, d_out_ptr, width, height, **kw):
         """spt_render_device: result stays in device memory at d_out_ptr (width*height*3 f32)."""

@@ -48,6 +48,7 @@ class WavefrontPathTracer:
         self.max_depth, self.pixel_sampler, self.filter = max_depth, pixel_sampler, filter
         self.seed, self.pool_size, self.flags = seed, pool_size, flags
         self.last_stats = None
+        self._comm = None
 
     def _kw(self, scene, config, rank=0, world=1):
         ps = self.pixel_sampler
@@ -68,11 +69,14 @@ class WavefrontPathTracer:
             self.last_stats = st
         else:
             import torch
+            from . import core
             rank, world = dist.get_rank(), dist.get_world_size()
             dev = torch.device("cuda", scene.ctx.device)
+            if self._comm is None:  # the library's own communicator: torch.distributed only hands the id round
+                self._comm = core.Comm.from_torch(scene.ctx)
             buf = torch.empty((config.height, config.width, 3), dtype=torch.float32, device=dev)
-            self.last_stats = scene.render_device(buf.data_ptr(), config.width, config.height, **self._kw(scene, config, rank, world))
-            dist.reduce(buf, dst=0, op=dist.ReduceOp.SUM)  # tiles are disjoint, other ranks hold zeros: exact
+            # every rank renders its tiles; only owned tiles travel (integer film, ncclSend/ncclRecv), rank 0 reconstructs the frame
+            self.last_stats = scene.render_gather(self._comm, buf.data_ptr(), config.width, config.height, root=0, **self._kw(scene, config, rank, world))
             if rank != 0:
                 return None
             img = buf.cpu().numpy()

@@ -253,6 +253,23 @@ def test_image_is_independent_of_kernel_scheduling(scene_pair, name):
             assert busy >= node and tri <= st2["tris_tested"]   # spheres count as primitive tests but have no triangle stage
 
 
+def test_render_gather_with_a_one_rank_communicator_equals_render_device(ctx, scene_pair):
+    """spt_comm_* / spt_render_gather on the degenerate one-rank communicator (NCCL is loaded and a communicator created, nothing
+    travels): the film is left unresolved by the render and reconstructed by the gather path — same frame as spt_render_device."""
+    import torch
+    from spt import core
+    fs, sc, _ = scene_pair("c2")
+    comm = core.Comm(ctx, core.Comm.unique_id(ctx.lib), 0, 1)
+    for radius in (0.5, 1.0):
+        a = torch.zeros((90, 160, 3), dtype=torch.float32, device="cuda")
+        b = torch.zeros_like(a)
+        st = sc.render_gather(comm, a.data_ptr(), 160, 90, spp=4, seed=2, filter_radius=radius)
+        sc.render_device(b.data_ptr(), 160, 90, spp=4, seed=2, filter_radius=radius)
+        torch.cuda.synchronize()
+        assert torch.equal(a, b) and st["paths"] == 160 * 90 * 4 and st["seconds_stage"][5] > 0
+    comm.close()
+
+
 def test_rgb8_encode_and_device_output(scene_pair):
     import torch
     fs, sc, _ = scene_pair("c1b")
