@@ -4,7 +4,7 @@ use std::process::Command;
 
 fn main() {
     let out = std::env::var("OUT_DIR").unwrap();
-    let src = ["spt_api.cu", "trav_kernels.cu", "shade_a.cu", "shade_b.cu", "shade_c.cu", "misc_kernels.cu", "bvh_build_gpu.cu", "flatten.cpp", "bvh_build.cpp"];
+    let src = ["spt_api.cu", "trav_kernels.cu", "shade_a.cu", "shade_b.cu", "shade_c.cu", "shade_a_lean.cu", "shade_b_lean.cu", "shade_c_lean.cu", "misc_kernels.cu", "bvh_build_gpu.cu", "flatten.cpp", "bvh_build.cpp"];
     let mut objs = vec![];
     for s in src {
         let o = format!("{}/{}.o", out, s);

@@ -184,6 +184,9 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
     for (int c = 0; c < 3; c++) o.emissive[c] = s.emissive[c];
     hs.surfaces[i] = o;
   }
+  hs.lean = true;
+  for (int i = 0; i < d.n_textures; i++) hs.lean = hs.lean && d.textures[i].tag == SPT_TEX_SCALAR;
+  for (int i = 0; i < d.n_surfaces; i++) hs.lean = hs.lean && d.surfaces[i].normal_map < 0 && d.surfaces[i].emissive_map < 0;
   // ---- spheres, meshes (+ BLAS) ------------------------------------------------------------------------------------
   hs.spheres.resize(d.n_spheres);
   for (int i = 0; i < d.n_spheres; i++) hs.spheres[i] = make_float4(d.spheres[i].center[0], d.spheres[i].center[1], d.spheres[i].center[2], d.spheres[i].radius);

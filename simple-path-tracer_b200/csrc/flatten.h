@@ -43,6 +43,7 @@ struct HostScene {
   int env_w = 0, env_h = 0;
   int light_sampler = 0, env_light_index = -1;
   bool has_image_tex = false;
+  bool lean = false;                // every texture is a plain scalar and no surface has a normal / emissive map: the SPT_LEAN shade kernels apply
   int64_t tlas_nodes = 0, blas_nodes = 0;
   double seconds_bvh = 0.0, seconds_create = 0.0; // build statistics (spt_scene_info)
   int64_t blas_on_device = 0;

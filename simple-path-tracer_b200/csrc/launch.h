@@ -8,6 +8,9 @@
 
 #define SPT_TRAV_BLOCK 128  // threads per block of every traversal / shade kernel
 #define SPT_LOGIC_BLOCK 256
+#ifndef SPT_SHADE_LEAN_MINB
+#define SPT_SHADE_LEAN_MINB 5 // resident blocks per SM the lean shade kernels are compiled for (and launched with: one wave)
+#endif
 #ifndef SPT_FETCH_CHUNK
 #define SPT_FETCH_CHUNK 32  // rays a warp reserves at a time with one atomic: caller ray batches
 #endif
@@ -32,7 +35,7 @@ void launch_batch(const DScene& sc, const float4* rays, uint32_t n, HitIO* hits,
                   bool any, bool count, int grid, cudaStream_t st);
 void launch_logic(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st);
 void launch_special(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st);
-void launch_shade(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st); // mat = -1: unsorted
+void launch_shade(int mat, const DScene& sc, const RenderParams& P, bool count, bool lean, int grid, cudaStream_t st); // mat = -1: unsorted (never lean)
 void launch_generate(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st);
 void launch_resolve(const long long* film, int n_pixels, float inv_spp, float* out_mean, uint8_t* out_rgb8, int grid, cudaStream_t st);
 void launch_resolve_box(const RenderParams& P, int k0, int n_k, float radius, int radius_int, float* out_mean, uint8_t* out_rgb8, int grid, cudaStream_t st);
@@ -44,4 +47,8 @@ void launch_bxdf(const DScene& sc, const SptBxdfQuery* q, long long n, SptBxdfRe
 void launch_shade_a(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st); // 0..3
 void launch_shade_b(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st); // 4..6
 void launch_shade_c(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st); // 7, -1
+// the same kernels compiled with SPT_LEAN (scenes whose textures are all plain scalars; shade_*_lean.cu)
+void launch_shade_a_lean(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st);
+void launch_shade_b_lean(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st);
+void launch_shade_c_lean(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st); // 7 only
 } // namespace spt

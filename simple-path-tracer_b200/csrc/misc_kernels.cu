@@ -332,9 +332,10 @@ void launch_aov_normal(const DScene& sc, const RenderParams& P, int grid, cudaSt
 void launch_bxdf(const DScene& sc, const SptBxdfQuery* q, long long n, SptBxdfResult* out, int grid, cudaStream_t st) {
   k_bxdf_batch<<<grid, SPT_BLOCK, 0, st>>>(sc, q, n, out);
 }
-void launch_shade(int mat, const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st) {
-  if (mat >= 0 && mat <= 3) launch_shade_a(mat, sc, P, count, grid, st);
-  else if (mat >= 4 && mat <= 6) launch_shade_b(mat, sc, P, count, grid, st);
+void launch_shade(int mat, const DScene& sc, const RenderParams& P, bool count, bool lean, int grid, cudaStream_t st) {
+  if (mat >= 0 && mat <= 3) { if (lean) launch_shade_a_lean(mat, sc, P, count, grid, st); else launch_shade_a(mat, sc, P, count, grid, st); }
+  else if (mat >= 4 && mat <= 6) { if (lean) launch_shade_b_lean(mat, sc, P, count, grid, st); else launch_shade_b(mat, sc, P, count, grid, st); }
+  else if (mat == 7 && lean) launch_shade_c_lean(mat, sc, P, count, grid, st);
   else launch_shade_c(mat, sc, P, count, grid, st);
 }
 } // namespace spt

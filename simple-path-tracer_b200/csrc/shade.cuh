@@ -112,11 +112,15 @@ SPT_D TexIn texin_from(const HitGeom& g) { // impl From<&Intersection> for Textu
 
 SPT_D float3 surface_emissive(const DScene& sc, const DSurface& s, const TexIn& in) { // surface.rs:49-55
   const float3 e = mk3(s.emissive[0], s.emissive[1], s.emissive[2]);
+#if SPT_LEAN
+  return e;
+#else
   return s.emissive_map >= 0 ? e * tex_color(sc, s.emissive_map, in) : e;
+#endif
 }
 SPT_D Frame surface_frame(const DScene& sc, const DSurface& s, float3 ray_d, const HitGeom& g, const TexIn& in) { // surface.rs:65-95
   float3 sn = g.n;
-  if (s.normal_map >= 0) {
+  if (!SPT_LEAN && s.normal_map >= 0) {
     const float3 v = tex_color(sc, s.normal_map, in) * 2.0f - mk3(1.f);
     const float3 nl = norm3(v);
     sn = norm3(nl.x * norm3(g.tan) + nl.y * norm3(g.bitan) + nl.z * g.n);

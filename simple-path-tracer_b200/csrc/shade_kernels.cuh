@@ -83,14 +83,21 @@ SPT_D void push_shadow(const RenderParams& P, const ShadowRay& sh, uint32_t pixe
 
 // ---- shade<MAT>: surface hits of one material class (pt.rs:112-193) --------------------------------------------------------------
 // Resident blocks per SM the shade kernels are compiled for (register budget = 65536 / (128 * min_blocks)).
-#ifdef SPT_SHADE_MINB
+#if SPT_LEAN
+// the lean kernels (texture.cuh: SPT_LEAN) need neither the TextureInput record nor the texture evaluator's stack frame: at 128
+// registers they do not spill at all, which leaves room for more resident blocks (measured: profiles/README.md, round 2)
+template <int MAT> struct ShadeCfg { static constexpr int min_blocks = SPT_SHADE_LEAN_MINB; };
+#elif defined(SPT_SHADE_MINB)
 template <int MAT> struct ShadeCfg { static constexpr int min_blocks = SPT_SHADE_MINB; };
 #else
 template <int MAT> struct ShadeCfg { static constexpr int min_blocks = 4; }; // measured best of 2..6 on every config
 #endif
 
-template <int MAT, bool COUNT>
+// LEAN only distinguishes the symbols of the two compilations of this kernel (shade_*.cu and shade_*_lean.cu); the body is selected
+// by the SPT_LEAN macro of the translation unit.
+template <int MAT, bool COUNT, int LEAN>
 __global__ void __launch_bounds__(SPT_BLOCK, ShadeCfg<MAT>::min_blocks) k_shade(const DScene sc, const RenderParams P) {
+  static_assert(LEAN == SPT_LEAN, "instantiate k_shade with LEAN = SPT_LEAN");
   constexpr bool PROBE = MAT < 0 || MAT == 7; // the BSSRDF probe ray needs the traversal stack
   __shared__ uint2 s_stack[PROBE ? SPT_SSTACK + SPT_WSTASH : 1][PROBE ? SPT_TRAV_BLOCK : 1];
   uint32_t nonfinite = 0, n_probe = 0, n_culled = 0;
@@ -122,7 +129,7 @@ __global__ void __launch_bounds__(SPT_BLOCK, ShadeCfg<MAT>::min_blocks) k_shade(
 
     HitGeom g;
     load_hit(sc, s.ro, s.rd, hit, g);
-    if (s.depth == 0 && sc.has_image_tex) { // ray differentials exist only for camera rays (Q18)
+    if (!SPT_LEAN && s.depth == 0 && sc.has_image_tex) { // ray differentials exist only for camera rays (Q18)
       const uint32_t k = s.sample;
       PathRng r2; r2.state = rng_init(P.seed, s.pixel, k);
       float ox, oy, x, y; pixel_offset(P, s.pixel, k, r2, ox, oy); film_xy(P, s.pixel, ox, oy, x, y);

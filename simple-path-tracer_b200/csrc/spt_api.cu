@@ -458,11 +458,12 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
     s->occ_bat = std::max(1, s->occ_bat);
     s->occ_ext = std::max(1, s->occ_ext); s->occ_con = std::max(1, s->occ_con);
   }
-  int grid_ext = 0, grid_con = 0, grid_shade = 0, grid_logic = 0, grid_gen = 0;
+  int grid_ext = 0, grid_con = 0, grid_shade = 0, grid_shade_lean = 0, grid_logic = 0, grid_gen = 0;
   auto set_active_pool = [&](int n) { // between iterations only: the queues are empty then, and slots never used are free slots
     P.pool.n = n;
     grid_ext = persistent_grid(s->ctx, n, s->occ_ext); grid_con = persistent_grid(s->ctx, n, s->occ_con);
     grid_shade = grid_for(s->ctx, n, 4); // = the resident blocks per SM (ShadeCfg::min_blocks): ONE wave of grid-stride blocks.  16 per SM cost 0.7 % (C2) .. 3.5 % (C3), 5 or 6 (a ragged second wave) 5-20 % of the shade stage
+    grid_shade_lean = grid_for(s->ctx, n, SPT_SHADE_LEAN_MINB);
     grid_logic = (n + SPT_LOGIC_BLOCK - 1) / SPT_LOGIC_BLOCK;
     grid_gen = std::min(grid_logic, s->ctx->sm_count * 8);
   };
@@ -471,6 +472,9 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   const bool timed = (r->flags & SPT_RENDER_TIME_STAGES) != 0;
   double stage[6] = {0, 0, 0, 0, 0, 0}; // generate (inside shade), extend, shade (logic..generate), connect, resolve, other
   const uint32_t mats = P.sort_materials ? ds.mat_mask : 0u;
+  // scenes whose textures are all plain scalars run the lean compilation of the shade kernels (SPT_SHADE_LEAN=0 forces the general one)
+  bool lean = s->hs.lean;
+  if (const char* e = getenv("SPT_SHADE_LEAN")) lean = lean && atoi(e) != 0;
   const bool special = ds.has_medium || ds.env_tex != nullptr;
   // Within one iteration the shade kernels of different material classes are independent of each other, and connect is
   // independent of generate + extend: they are issued on separate streams so that small kernels overlap and the tail of
@@ -490,8 +494,8 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
     spt::launch_logic(ds, P, grid_logic, st); launches++;
     if (special) { spt::launch_special(ds, P, grid_shade, st); launches++; }
     if (serial) {
-      for (int m = 0; m < 8; m++) if (mats & (1u << m)) { spt::launch_shade(m, ds, P, count, grid_shade, st); launches++; }
-      if (!P.sort_materials) { spt::launch_shade(-1, ds, P, count, grid_shade, st); launches++; }
+      for (int m = 0; m < 8; m++) if (mats & (1u << m)) { spt::launch_shade(m, ds, P, count, lean, lean ? grid_shade_lean : grid_shade, st); launches++; }
+      if (!P.sort_materials) { spt::launch_shade(-1, ds, P, count, false, grid_shade, st); launches++; }
       spt::launch_generate(ds, P, grid_gen, st); launches++;
       if (timed) cudaEventRecord(s->sev[1], st);
       spt::launch_connect(ds, P, count, grid_con, st);
@@ -503,9 +507,9 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
       for (int m = 0; m < 8; m++) if (mats & (1u << m)) {
         cudaStream_t sm = st;
         if (k > 0) { const int j = (k - 1) & 1; sm = s->aux[j]; if (!used[j]) { cudaStreamWaitEvent(sm, s->ev_fork, 0); used[j] = true; } }
-        spt::launch_shade(m, ds, P, count, grid_shade, sm); launches++; k++;
+        spt::launch_shade(m, ds, P, count, lean, lean ? grid_shade_lean : grid_shade, sm); launches++; k++;
       }
-      if (!P.sort_materials) { spt::launch_shade(-1, ds, P, count, grid_shade, st); launches++; }
+      if (!P.sort_materials) { spt::launch_shade(-1, ds, P, count, false, grid_shade, st); launches++; }
       for (int j = 0; j < 2; j++) if (used[j]) { cudaEventRecord(s->ev_join[j], s->aux[j]); cudaStreamWaitEvent(st, s->ev_join[j], 0); }
       cudaEventRecord(s->ev_shaded, st);
       cudaStreamWaitEvent(s->aux[2], s->ev_shaded, 0);

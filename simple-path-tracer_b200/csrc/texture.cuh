@@ -123,10 +123,20 @@ __device__ __noinline__ float4 tex_eval_d(const DScene& sc, int id, TexIn in) {
   if (srgb) r = make_float4(srgb_lin(r.x), srgb_lin(r.y), srgb_lin(r.z), r.w);
   return r;
 }
+// SPT_LEAN (a second compilation of the shade kernels, launched for scenes whose textures are all plain scalars and whose surfaces have
+// no normal / emissive map — every benchmark config): a texture IS its value, so the expression-tree evaluator, the TextureInput
+// record it takes by value and the camera-ray differentials that feed it drop out of the kernels.
+#ifndef SPT_LEAN
+#define SPT_LEAN 0
+#endif
 SPT_D float4 tex_eval(const DScene& sc, int id, const TexIn& in) {
   const DTexture& t = sc.textures[id];
+#if SPT_LEAN
+  return make_float4(t.value[0], t.value[1], t.value[2], 1.0f);
+#else
   if (t.tag == 0) return make_float4(t.value[0], t.value[1], t.value[2], 1.0f); // fast path: every benchmark scene
   return tex_eval_d<SPT_TEX_MAX_DEPTH>(sc, id, in);
+#endif
 }
 SPT_D float3 tex_color(const DScene& sc, int id, const TexIn& in) { return mk3(tex_eval(sc, id, in)); }
 SPT_D float tex_float(const DScene& sc, int id, const TexIn& in, int chan) {
