@@ -9,7 +9,7 @@
 #define SPT_TRAV_BLOCK 128  // threads per block of every traversal / shade kernel
 #define SPT_LOGIC_BLOCK 256
 #ifndef SPT_SHADE_LEAN_MINB
-#define SPT_SHADE_LEAN_MINB 5 // resident blocks per SM the lean shade kernels are compiled for (and launched with: one wave)
+#define SPT_SHADE_LEAN_MINB 4 // resident blocks per SM the lean shade kernels are compiled for (and launched with: one wave).  Measured 4 / 5 / 6: C2 shade stage 22.1 / 23.4 / 23.6 ms (general kernels: 27.2)
 #endif
 #ifndef SPT_FETCH_CHUNK
 #define SPT_FETCH_CHUNK 32  // rays a warp reserves at a time with one atomic: caller ray batches

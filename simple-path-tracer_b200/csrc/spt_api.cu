@@ -471,6 +471,10 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   uint64_t iters = 0, launches = 0;
   const bool timed = (r->flags & SPT_RENDER_TIME_STAGES) != 0;
   double stage[6] = {0, 0, 0, 0, 0, 0}; // generate (inside shade), extend, shade (logic..generate), connect, resolve, other
+  // SPT_TRACE_ITERS=file (with SPT_RENDER_TIME_STAGES): one line per iteration — iteration, active pool, live paths, sample cursor,
+  // shadow rays, ms of logic..generate / connect / extend — the fill / steady / drain profile of a render (tools/share_profile.py)
+  FILE* trace = nullptr;
+  if (timed) if (const char* e = getenv("SPT_TRACE_ITERS")) trace = fopen(e, "a");
   const uint32_t mats = P.sort_materials ? ds.mat_mask : 0u;
   // scenes whose textures are all plain scalars run the lean compilation of the shade kernels (SPT_SHADE_LEAN=0 forces the general one)
   bool lean = s->hs.lean;
@@ -563,12 +567,14 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
         float a = 0, b = 0, c = 0;
         cudaEventElapsedTime(&a, s->sev[0], s->sev[1]); cudaEventElapsedTime(&b, s->sev[1], s->sev[2]); cudaEventElapsedTime(&c, s->sev[2], s->sev[3]);
         stage[2] += a * 1e-3; stage[3] += b * 1e-3; stage[1] += c * 1e-3;
+        if (trace) fprintf(trace, "%llu %d %u %llu %u %.4f %.4f %.4f\n", (unsigned long long)iters, P.pool.n, s->h_ctr->it.live, s->h_ctr->cursor, s->h_ctr->it.sq, a, b, c);
       }
       // done = nothing in flight AND every camera sample started: an iteration can end with no live path while samples remain
       // (all of its ordinals fell into the padding of edge tiles, or max_depth ended every path it started)
       if (s->h_ctr->it.live == 0 && s->h_ctr->cursor >= P.total_samples) break;
     }
   }
+  if (trace) fclose(trace);
   s->last_P = P;
   if (d_mean) { resolve_film(s, r->filter_radius, d_mean, d_rgb8, st); launches++; }
   CU(cudaEventRecord(s->ev[1], st));

@@ -196,6 +196,9 @@ struct SimCfg {
   int32_t max_pass;     // passes per stage and round in the slot design
   int32_t pop_end;      // 1: a second pop stage at the END of the round (a ray that has nothing left finishes in the round of its last test)
   int32_t order;        // 0: node, inst, tri   1: inst, node, tri   2: inst, node, inst, tri
+  int32_t gate_leaf;    // one-ray-per-lane design: the instance / triangle stages run only when at least this many lanes want them, or the
+                        // stage was skipped in the previous gate_wait rounds
+  int32_t gate_wait;
   int32_t gate;         // slot design: a pass of a stage only runs when at least this many slots need it (or nothing else can run)
   float c_round, c_pop, c_node, c_inst, c_tri, c_tri_dist; // warp-instructions per executed stage
   float c_tri_setup;    // tri_dist 1: once per round that has triangle work
@@ -220,7 +223,7 @@ int sim_run(void* scene, const SptRay* rays, int64_t n, const SimCfg* cfg, SimOu
   Sim S(hs, cfg->any != 0);
   const int NW = std::max(1, cfg->n_warps);
   const int NS = std::max(32, cfg->slots);
-  struct Warp { std::vector<Lane> lane; int64_t w_next = 0, w_end = 0; bool exhausted = false, done = false; };
+  struct Warp { std::vector<Lane> lane; int64_t w_next = 0, w_end = 0; bool exhausted = false, done = false; int skipped_inst = 0, skipped_tri = 0; };
   std::vector<Warp> warps(NW);
   for (auto& W : warps) W.lane.resize(NS);
   int64_t cursor = 0;
@@ -279,9 +282,21 @@ int sim_run(void* scene, const SptRay* rays, int64_t n, const SimCfg* cfg, SimOu
         gated = std::max(cn, std::max(ci, ct)) >= cfg->gate;
       }
       stage(w_pop, [&](Lane& L) { return S.pop(L); }, cfg->c_pop, st_pop, a_pop, slot_design ? 2 : 1, false);
+      auto count_want = [&](auto want) { int c = 0; for (int m = 0; m < NS; m++) c += W.lane[m].has && !fin[m] && want(W.lane[m]); return c; };
+      bool run_inst = true, run_tri = true;
+      if (!slot_design && cfg->gate_leaf > 1) {
+        const int ci = count_want(w_inst);
+        run_inst = ci >= cfg->gate_leaf || W.skipped_inst >= cfg->gate_wait || ci == 0;
+        W.skipped_inst = run_inst ? 0 : W.skipped_inst + 1;
+      }
       if (cfg->order >= 1) stage(w_inst, [&](Lane& L) { return S.inst(L); }, cfg->c_inst, st_inst, a_inst, P, true);
       stage(w_node, [&](Lane& L) { S.node(L); return false; }, cfg->c_node, st_node, a_node, P, true);
-      if (cfg->order != 1) stage(w_inst, [&](Lane& L) { return S.inst(L); }, cfg->c_inst, st_inst, a_inst, P, true);
+      if (cfg->order != 1 && run_inst) stage(w_inst, [&](Lane& L) { return S.inst(L); }, cfg->c_inst, st_inst, a_inst, P, true);
+      if (!slot_design && cfg->gate_leaf > 1) {
+        const int ct = count_want(w_tri);
+        run_tri = ct >= cfg->gate_leaf || W.skipped_tri >= cfg->gate_wait || ct == 0;
+        W.skipped_tri = run_tri ? 0 : W.skipped_tri + 1;
+      }
       if (cfg->tri_dist == 2) {
         // helper passes: every lane with pending triangles tests its first one; lanes WITHOUT triangle work take the second triangle of
         // the i-th lane that has two or more (ballot matching, ray handed over by shuffles).  tri_per_round passes at most.
@@ -296,7 +311,7 @@ int sim_run(void* scene, const SptRay* rays, int64_t n, const SimCfg* cfg, SimOu
           cost += cfg->c_tri_dist; use += cfg->c_tri_dist * (owners + helped) / 32.0; st_tri++; a_tri += owners + helped; tri_passes++;
         }
       } else if (!cfg->tri_dist) {
-        stage(w_tri, [&](Lane& L) { return S.tri(L); }, cfg->c_tri, st_tri, a_tri, slot_design ? P * 2 : cfg->tri_per_round, true);
+        if (run_tri) stage(w_tri, [&](Lane& L) { return S.tri(L); }, cfg->c_tri, st_tri, a_tri, slot_design ? P * 2 : cfg->tri_per_round, true);
       } else {
         std::vector<std::pair<int, uint32_t>> work;
         for (int l = 0; l < NS; l++) { Lane& L = W.lane[l]; if (L.has && !fin[l] && w_tri(L)) {

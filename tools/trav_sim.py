@@ -17,7 +17,7 @@ LIB = os.path.join(ROOT, "tools", "_build", "libtravsim.so")
 
 
 class Cfg(C.Structure):
-    _fields_ = [(k, C.c_int32) for k in ("any", "n_warps", "chunk", "min_idle", "tri_per_round", "tri_dist", "node_twice", "inst_dist", "slots", "max_pass", "pop_end", "order", "gate")] + \
+    _fields_ = [(k, C.c_int32) for k in ("any", "n_warps", "chunk", "min_idle", "tri_per_round", "tri_dist", "node_twice", "inst_dist", "slots", "max_pass", "pop_end", "order", "gate_leaf", "gate_wait", "gate")] + \
                [(k, C.c_float) for k in ("c_round", "c_pop", "c_node", "c_inst", "c_tri", "c_tri_dist", "c_tri_setup", "c_slot")]
 
 
@@ -84,15 +84,16 @@ def shadow_mix(fs, n, seed=3):
     return np.ascontiguousarray(d1[:n])
 
 
-BASE = dict(any=0, n_warps=48, chunk=64, min_idle=6, tri_per_round=2, tri_dist=0, node_twice=0, inst_dist=0, slots=32, max_pass=1, pop_end=0, order=0, gate=1,
+BASE = dict(any=0, n_warps=48, chunk=64, min_idle=6, tri_per_round=2, tri_dist=0, node_twice=0, inst_dist=0, slots=32, max_pass=1, pop_end=0, order=0, gate_leaf=1, gate_wait=1, gate=1,
             c_round=45.0, c_pop=25.0, c_node=250.0, c_inst=110.0, c_tri=75.0, c_tri_dist=110.0, c_tri_setup=50.0, c_slot=30.0)
 VARIANTS = {
-    "current": {},
-    "pop_end idle3": dict(pop_end=1, min_idle=3),
-    "smem dist": dict(tri_dist=1, pop_end=1, min_idle=3),
-    "helper x1 (c=100)": dict(tri_dist=2, pop_end=1, min_idle=3, tri_per_round=1, c_tri_dist=100.0),
-    "helper x2 (c=100)": dict(tri_dist=2, pop_end=1, min_idle=3, tri_per_round=2, c_tri_dist=100.0),
-    "helper x2 (c=110)": dict(tri_dist=2, pop_end=1, min_idle=3, tri_per_round=2, c_tri_dist=110.0),
+    "round1": {},
+    "pop_end (now)": dict(pop_end=1),
+    "gate 8 wait 1": dict(pop_end=1, gate_leaf=8, gate_wait=1),
+    "gate 8 wait 2": dict(pop_end=1, gate_leaf=8, gate_wait=2),
+    "gate 12 wait 2": dict(pop_end=1, gate_leaf=12, gate_wait=2),
+    "gate 12 wait 3": dict(pop_end=1, gate_leaf=12, gate_wait=3),
+    "gate 16 wait 3": dict(pop_end=1, gate_leaf=16, gate_wait=3),
 }
 
 if __name__ == "__main__":
