@@ -315,6 +315,17 @@ int32_t spt_trace_batch_device(SptScene* scene, const SptRay* d_rays, int64_t n,
 int32_t spt_occluded_batch_device(SptScene* scene, const SptRay* d_rays, int64_t n, uint8_t* d_out,
                                   uint32_t flags, SptStats* stats, void* stream);
 
+/* spt_trace_batch without any allocation.  NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs and
+ * results as spt_trace_batch (host buffers), for n <= SPT_NOALLOC_MAX_RAYS rays per call; a larger n returns SPT_ERR_INVALID with a
+ * message naming the limit.  The device scratch the batch needs (ray staging, hit staging, the fetch cursor: 3.3 MB) lives in a
+ * file-scope device array that every GPU loading the library holds until exit; the call performs no cudaMalloc / cudaFree and calls no
+ * allocating library routine.  All calls on a device share that array, which keeps the last call's contents (the call clears what
+ * must start at zero): calls that overlap on the GPU would race, so the call synchronises before it returns and must not be issued
+ * from two host threads at once. */
+#define SPT_NOALLOC_MAX_RAYS 65536
+int32_t spt_trace_batch_noalloc(SptScene* scene, const SptRay* rays, int64_t n, SptHit* out_hits);
+
 /* Test hook ≙ BxdfT::{sample,pdf,bxdf,is_delta} with caller-supplied random numbers. */
 int32_t spt_bxdf_batch(SptScene* scene, const SptBxdfQuery* queries, int64_t n, SptBxdfResult* out);
 

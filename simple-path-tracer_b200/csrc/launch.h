@@ -33,6 +33,8 @@ void launch_extend(const DScene& sc, const RenderParams& P, bool count, int grid
 void launch_connect(const DScene& sc, const RenderParams& P, bool count, int grid, cudaStream_t st);
 void launch_batch(const DScene& sc, const float4* rays, uint32_t n, HitIO* hits, uint8_t* occ, uint32_t* next, DevCounters* ctr,
                   bool any, bool count, int grid, cudaStream_t st);
+// the no-allocation ray batch (trav_kernels.cu: scratch in a file-scope device array of SPT_NOALLOC_MAX_RAYS rays)
+cudaError_t trace_batch_noalloc(const DScene& sc, const SptRay* h_rays, uint32_t n, SptHit* h_hits, int grid, cudaStream_t st);
 void launch_logic(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st);
 void launch_special(const DScene& sc, const RenderParams& P, int grid, cudaStream_t st);
 void launch_shade(int mat, const DScene& sc, const RenderParams& P, bool count, bool lean, int grid, cudaStream_t st); // mat = -1: unsorted (never lean)

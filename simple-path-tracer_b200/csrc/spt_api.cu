@@ -309,6 +309,21 @@ static int32_t batch_host(SptScene* s, const SptRay* rays, int64_t n, void* out,
 int32_t spt_trace_batch(SptScene* s, const SptRay* rays, int64_t n, SptHit* out) { return batch_host(s, rays, n, out, sizeof(SptHit), false); }
 int32_t spt_occluded_batch(SptScene* s, const SptRay* rays, int64_t n, uint8_t* out) { return batch_host(s, rays, n, out, 1, true); }
 
+// No counterpart in the reference (see spt.h).  Allocates nothing: the scratch is a
+// file-scope device array in trav_kernels.cu.
+int32_t spt_trace_batch_noalloc(SptScene* s, const SptRay* rays, int64_t n, SptHit* out) {
+  if (!s || n < 0 || (n > 0 && (!rays || !out))) return fail(SPT_ERR_INVALID, "spt_trace_batch_noalloc: bad argument");
+  if (n > SPT_NOALLOC_MAX_RAYS)
+    return fail(SPT_ERR_INVALID, "spt_trace_batch_noalloc: n = " + std::to_string(n) + " exceeds SPT_NOALLOC_MAX_RAYS = " + std::to_string(SPT_NOALLOC_MAX_RAYS) +
+                                 " (the fixed scratch array); split the batch or use spt_trace_batch");
+  if (n == 0) return SPT_OK;
+  CU(cudaSetDevice(s->ctx->device));
+  if (!s->occ_bat) { CU(spt::occupancy_traversal(&s->occ_ext, &s->occ_con, &s->occ_bat)); s->occ_bat = std::max(1, s->occ_bat); }
+  const cudaError_t e = spt::trace_batch_noalloc(s->ds, rays, (uint32_t)n, out, persistent_grid(s->ctx, n, s->occ_bat), s->stream);
+  if (e != cudaSuccess) return fail(SPT_ERR_CUDA, std::string("spt_trace_batch_noalloc: ") + cudaGetErrorString(e));
+  return SPT_OK;
+}
+
 } // extern "C"
 
 extern "C" int32_t spt_bxdf_batch(SptScene* s, const SptBxdfQuery* queries, int64_t n, SptBxdfResult* out) {

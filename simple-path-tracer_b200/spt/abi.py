@@ -140,7 +140,9 @@ SYMBOLS = ["spt_last_error", "spt_version", "spt_context_create", "spt_context_d
            "spt_scene_upload", "spt_scene_info", "spt_scene_destroy", "spt_trace_batch", "spt_occluded_batch",
            "spt_trace_batch_device", "spt_occluded_batch_device", "spt_bxdf_batch", "spt_render",
            "spt_render_device", "spt_film_save", "spt_film_load", "spt_owned_tiles",
-           "spt_comm_unique_id", "spt_comm_create", "spt_comm_destroy", "spt_render_gather"]
+           "spt_comm_unique_id", "spt_comm_create", "spt_comm_destroy", "spt_render_gather",
+           "spt_trace_batch_noalloc"]
+NOALLOC_MAX_RAYS = 65536
 COMM_ID_BYTES = 128
 
 PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -174,6 +176,7 @@ def load_library(path=None):
         "spt_scene_destroy": [vp],
         "spt_trace_batch": [vp, vp, C.c_int64, vp],
         "spt_occluded_batch": [vp, vp, C.c_int64, vp],
+        "spt_trace_batch_noalloc": [vp, vp, C.c_int64, vp],
         "spt_trace_batch_device": [vp, vp, C.c_int64, vp, C.c_uint32, P(Stats), vp],
         "spt_occluded_batch_device": [vp, vp, C.c_int64, vp, C.c_uint32, P(Stats), vp],
         "spt_bxdf_batch": [vp, vp, C.c_int64, vp],

@@ -96,6 +96,14 @@ class Scene:
         abi.check(self.lib, self.lib.spt_trace_batch(self.h, rays.ctypes.data, len(rays), hits.ctypes.data))
         return hits
 
+    def trace_noalloc(self, rays):
+        """spt_trace_batch_noalloc: spt_trace_batch for at most abi.NOALLOC_MAX_RAYS rays, with its device scratch in a fixed
+        file-scope array — no allocation on the call path."""
+        rays = np.ascontiguousarray(rays, RAY_DT)
+        hits = np.zeros(len(rays), HIT_DT)
+        abi.check(self.lib, self.lib.spt_trace_batch_noalloc(self.h, rays.ctypes.data, len(rays), hits.ctypes.data))
+        return hits
+
     def occluded(self, rays):
         rays = np.ascontiguousarray(rays, RAY_DT)
         out = np.zeros(len(rays), np.uint8)
