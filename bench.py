@@ -282,13 +282,20 @@ def main():
     ext_seconds = s0["seconds_stage"][1]
     rays_per_launch = s0["ext_rays"] / max(1, ext_launches)
     achieved = rays_per_launch * b_ray / max(ext_seconds / max(1, ext_launches), 1e-12) / 1e9
-    traffic = None
-    try:  # dram__bytes_read.sum + dram__bytes_write.sum of one k_extend launch from the committed ncu --set full capture
-        with open(os.path.join(ROOT, "profiles", "r01_ncu_extend_traffic.json")) as fh:
-            cap = json.load(fh)  # captured at a 2^22-slot pool: DRAM bytes per ray of that launch x the rays per launch of this run
+    # DRAM traffic and issue statistics of k_extend cannot be measured from inside a run (they need the profiler): they come from the
+    # committed `ncu --set full` capture of one steady-state launch of this same command (profiles/r02_ncu_extend.json, made by
+    # tools/gpu_profile.sh + tools/ncu_extract.py; it names the commit it was taken at).  `traffic` = its DRAM bytes per ray x the rays
+    # per launch of THIS run; everything else in the roofline block is measured live.
+    traffic, cap = None, None
+    for name in ("r02_ncu_extend.json", "r01_ncu_extend_traffic.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as fh:
+                cap = json.load(fh)
             traffic = cap["dram_bytes_per_launch"] / cap["rays_in_captured_launch"] * rays_per_launch
-    except (OSError, KeyError):
-        pass
+            cap["file"] = "profiles/" + name
+            break
+        except (OSError, KeyError):
+            cap = None
     # regime (i) of SURVEY §8d: the scene is L2-resident, so the node / triangle / instance fetches are bounded by the
     # L2 -> SM read bandwidth, measured here with a 16-byte-load microbenchmark over a 32 MB read-only set
     l2 = None
@@ -317,8 +324,14 @@ def main():
                 "grays_per_s": rays_per_launch / max(ext_seconds / max(1, ext_launches), 1e-12) / 1e9,
                 "stage_seconds": {"extend": s0["seconds_stage"][1], "shade": s0["seconds_stage"][2], "connect": s0["seconds_stage"][3],
                                   "total": s0["seconds_total"]},
+                "traffic_source": None if cap is None else {"file": cap["file"], "commit": cap.get("commit"), "dram_bytes_per_ray": cap["dram_bytes_per_launch"] / cap["rays_in_captured_launch"],
+                                                            "how": "ncu --set full capture of one steady-state k_extend launch, scaled per ray to this run's rays per launch (not measured in this run)"},
+                "issue": None if cap is None or "lanes_per_inst" not in cap else {
+                    "what": "the binding roof: instruction issue (same ncu capture)", "commit": cap.get("commit"), "issue_active_pct": cap.get("issue_active_pct"),
+                    "lanes_per_inst": cap.get("lanes_per_inst"), "alu_pipe_pct": cap.get("alu_pipe_pct"), "xu_pipe_pct": cap.get("xu_pipe_pct"),
+                    "fma_pipe_pct": cap.get("fma_pipe_pct"), "warps_active_pct": cap.get("warps_active_pct"), "l1_hit_pct": cap.get("l1_hit_pct")},
                 "l2": l2,
-                "note": "scene working set (%.2f MB) is L2-resident: the HBM figure is the contract's denominator, the binding roof is instruction issue (ncu: issue-active 72 %%, ALU pipe 50 %%, XU 52 %%, 14/32 active lanes)" % (info["bytes_total"] / 1e6)}
+                "note": "scene working set (%.2f MB) is L2-resident: the HBM figure is the contract's denominator; neither memory roof binds, the kernel is bound by instruction issue (see `issue`)" % (info["bytes_total"] / 1e6)}
     out = {
         "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": W,
         "ms_per_step": 1e3 * elapsed / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,

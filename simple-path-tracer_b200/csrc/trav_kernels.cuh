@@ -16,7 +16,8 @@ struct ExtendSrc { // every live path of the pool: closest hit (pt.rs:49-50)
   const RenderParams& P;
   uint32_t n_rays;
   uint32_t n_list; // 0: scan the pool slots; > 0 (draining pool): the live slots are listed in P.ext_queue[0 .. n_list)
-  static constexpr uint32_t kChunk = SPT_EXTEND_CHUNK;
+  uint32_t chunk_;
+  SPT_D uint32_t chunk() const { return chunk_; }
   SPT_D uint32_t total() const { return n_list ? n_list : (uint32_t)P.pool.n; }
   SPT_D uint32_t slot_of(uint32_t i) const { return n_list ? P.ext_queue[i] : i; }
   SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
@@ -36,7 +37,8 @@ struct ExtendSrc { // every live path of the pool: closest hit (pt.rs:49-50)
 struct ConnectSrc { // the queued shadow rays: any hit (pt.rs:81, :169); unoccluded contributions go to the film
   const RenderParams& P;
   uint32_t n, nonfinite;
-  static constexpr uint32_t kChunk = SPT_CONNECT_CHUNK;
+  uint32_t chunk_;
+  SPT_D uint32_t chunk() const { return chunk_; }
   SPT_D uint32_t total() const { return n; }
   SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
     const float4 o4 = P.sq.o[i], d4 = P.sq.d[i];
@@ -47,6 +49,18 @@ struct ConnectSrc { // the queued shadow rays: any hit (pt.rs:81, :169); unocclu
     if (h.inst < 0) { const float4 c = P.sq.c[i]; film_add(P, __float_as_uint(c.w), mk3(c), nonfinite); }
   }
 };
+
+// Rays a warp reserves per atomic.  With plenty of work the measured optimum (SPT_EXTEND_CHUNK / SPT_CONNECT_CHUNK = 64); when a launch
+// holds fewer rays than that gives every warp of the grid (a draining pool, the last iterations of a render) the launch is
+// latency-bound — its duration is the time of the warp with the most rays — so the rays are spread over all warps, down to
+// SPT_MIN_CHUNK per warp.
+#ifndef SPT_MIN_CHUNK
+#define SPT_MIN_CHUNK 8
+#endif
+SPT_D uint32_t spread_chunk(uint32_t n_rays, uint32_t full) {
+  const uint32_t warps = gridDim.x * (SPT_BLOCK / 32);
+  return max((uint32_t)SPT_MIN_CHUNK, min(full, (n_rays + warps - 1) / warps));
+}
 
 // Tuning builds may force a register budget with -DSPT_TRAV_MINB=n (resident blocks per SM).  Measured on C2/C3/C5: the
 // unconstrained allocation (72 registers, 7 blocks/SM) beats both n=8 (64 registers, -2 %) and n=1 (-18 %).
@@ -59,8 +73,9 @@ struct ConnectSrc { // the queued shadow rays: any hit (pt.rs:81, :169); unocclu
 template <bool COUNT>
 __global__ void SPT_TRAV_BOUNDS k_extend(const DScene sc, const RenderParams P) {
   TravCounters tc = {};
-  ExtendSrc src{P, 0, P.ctr->it.drain ? P.ctr->it.n_ext : 0u};
+  ExtendSrc src{P, 0, P.ctr->it.drain ? P.ctr->it.n_ext : 0u, SPT_EXTEND_CHUNK};
   if (P.ctr->it.drain && src.n_list == 0u) return; // a draining pool without a live path
+  if (src.n_list) src.chunk_ = spread_chunk(src.n_list, SPT_EXTEND_CHUNK);
   trace_persistent<false, COUNT>(sc, src, &P.ctr->it.next_ext, tc);
   warp_sum_to(&P.ctr->ext_rays, src.n_rays);
   if (COUNT) flush_trav_counters(P.ctr, tc);
@@ -69,7 +84,8 @@ __global__ void SPT_TRAV_BOUNDS k_extend(const DScene sc, const RenderParams P) 
 template <bool COUNT>
 __global__ void SPT_TRAV_BOUNDS k_connect(const DScene sc, const RenderParams P) {
   TravCounters tc = {};
-  ConnectSrc src{P, P.ctr->it.sq, 0};
+  ConnectSrc src{P, P.ctr->it.sq, 0, SPT_CONNECT_CHUNK};
+  src.chunk_ = spread_chunk(src.n, SPT_CONNECT_CHUNK);
   trace_persistent<true, COUNT>(sc, src, &P.ctr->it.next_con, tc);
   if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&P.ctr->shadow_rays, (unsigned long long)src.n);
   warp_sum_to(&P.ctr->nonfinite, src.nonfinite);
@@ -84,7 +100,7 @@ struct BatchSrc {
   uint32_t n;
   HitIO* __restrict__ hits;       // closest-hit output or null
   uint8_t* __restrict__ occ;      // any-hit output or null
-  static constexpr uint32_t kChunk = SPT_FETCH_CHUNK;
+  SPT_D uint32_t chunk() const { return SPT_FETCH_CHUNK; }
   SPT_D uint32_t total() const { return n; }
   SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
     const float4 a = ldg4(rays + 2 * (size_t)i), b = ldg4(rays + 2 * (size_t)i + 1);

@@ -389,7 +389,7 @@ SPT_D bool traverse(const DScene& sc, float3 ow, float3 dw, float tmin, HitRec& 
 }
 
 // Persistent-warp driver.  Src provides
-//   static constexpr uint32_t kChunk;                                  candidates a warp reserves at a time (one atomic)
+//   uint32_t chunk() const;                                            candidates a warp reserves at a time (one atomic); warp-uniform
 //   uint32_t total() const;                                            number of candidate rays of this launch
 //   bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax);   false: nothing to trace at i
 //   void store(uint32_t i, const HitRec& h);                           closest hit (inst = -1: miss) / ANY: inst = 0 occluded
@@ -443,15 +443,15 @@ SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCoun
     if (idle == FULL || __popc(idle) >= SPT_FETCH_MIN_IDLE) {
       if (w_next >= w_end && !exhausted) { // next chunk of this warp
 #if SPT_FETCH_STATIC
-        const uint32_t base = chunk * (uint32_t)Src::kChunk; // chunks dealt round-robin over the warps of the grid: no atomics
+        const uint32_t base = chunk * src.chunk(); // chunks dealt round-robin over the warps of the grid: no atomics
         chunk += gridDim.x * (SPT_TRAV_BLOCK / 32);
 #else
         uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(next, (uint32_t)Src::kChunk);
+        if (lane == 0) base = atomicAdd(next, src.chunk());
         base = __shfl_sync(FULL, base, 0);
 #endif
         if (base >= total) exhausted = true;
-        else { w_next = base; w_end = min(base + (uint32_t)Src::kChunk, total); }
+        else { w_next = base; w_end = min(base + src.chunk(), total); }
       }
       const uint32_t avail = w_end - w_next; // w_end >= w_next always
       const uint32_t take = min((uint32_t)__popc(idle), avail);
