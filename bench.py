@@ -155,6 +155,7 @@ def main():
     ap.add_argument("--pool", type=int, default=0)
     ap.add_argument("--ref-seconds", type=float, default=8.0, help="CPU seconds per reference/cpu_baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the secondary C5 @ 512 spp figure (about 10 s on one GPU)")
     ap.add_argument("--no-parity", action="store_true", help="skip the converged-image parity block (about 30 s of CPU oracle)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -264,6 +265,39 @@ def main():
         sampler.stop_flag = True
         sampler.join(timeout=2)
 
+    # ---- secondary figure on the north star's own multi-GPU config (all ranks): C5 = 2000 instanced bunnies at 3840x2160, 512 of its
+    # 4096 spp (paths/s is spp-invariant at this length: 4.2 G samples).  The headline stays C2 so that every N reports the same workload.
+    scale_c5 = None
+    if args.workload == "c2" and not args.no_secondary:
+        c5cfg = scenes.CONFIGS["c5"]
+        w5, h5, spp5 = c5cfg["width"], c5cfg["height"], 512
+        sc5 = core.Scene(ctx, scenes.load("c5"))
+        fb5 = torch.zeros((h5, w5, 3), dtype=torch.float32, device=dev)
+        kw5 = dict(spp=spp5, max_depth=8, sampler="recurrence")
+
+        def step5(seed):
+            if world > 1:
+                return sc5.render_gather(comm, fb5.data_ptr(), w5, h5, root=0, seed=seed, **kw5)
+            return sc5.render_device(fb5.data_ptr(), w5, h5, seed=seed, **kw5)
+
+        step5(50)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        st5 = step5(51)
+        e1.record()
+        barrier()
+        t5 = torch.tensor([e0.elapsed_time(e1) * 1e-3], dtype=torch.float64, device=dev)
+        a5 = torch.tensor([st5["paths"], st5["ext_rays"] + st5["shadow_rays"] + st5["probe_rays"]], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t5, op=dist.ReduceOp.MAX)
+            dist.all_reduce(a5, op=dist.ReduceOp.SUM)
+        scale_c5 = {"workload": f"c5: {w5}x{h5} @ {spp5} of its 4096 spp, 2000 instances x bunny_5k = 10.0 M instanced triangles, max_depth 8",
+                    "value": float(a5[0].item()) / float(t5.item()) / 1e6, "unit": "Mpaths/s", "mrays_per_s": float(a5[1].item()) / float(t5.item()) / 1e6,
+                    "ms_per_frame": 1e3 * float(t5.item()), "steps": 1, "warmup": 1, "n_gpus": world}
+        sc5.close()
+        del fb5
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -343,7 +377,7 @@ def main():
         "mrays_per_s": mrays, "rays_per_path": (ext + shadow + probe) / paths,
         "shadow_rays_culled_per_path": sum(s["shadow_culled"] for s in stats) / max(1.0, sum(s["paths"] for s in stats)),
         "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(w * h * 3 * 4)},
-        "gpu_launches": int(launches), "roofline": roofline, "clocks": sampler.summary() if sampler else None,
+        "gpu_launches": int(launches), "scale_c5": scale_c5, "roofline": roofline, "clocks": sampler.summary() if sampler else None,
         "timing": {"source": "CUDA events bracketing the K steps, max over ranks", "wall_ms_per_step": float(max(b[2] for b in brk_list)),
                    "render_device_ms_per_rank": [round(float(b[0]), 3) for b in brk_list],
                    "gather_ms_per_rank": [round(float(b[1]), 3) for b in brk_list],

@@ -3,9 +3,9 @@
 #   2. ncu --set full with source counters of one steady-state k_extend, k_connect and the k_shade launches of an iteration (C2, 8 spp)
 TAG=${TAG:-r02}
 set -x
-python bench.py --spp 64 --steps 1 --warmup 3 --no-parity --no-cpu-baseline > gpurun_out/${TAG}_bench_64spp_plain.json 2>/dev/null || exit 1
+python bench.py --spp 64 --steps 1 --warmup 3 --no-parity --no-cpu-baseline --no-secondary > gpurun_out/${TAG}_bench_64spp_plain.json 2>/dev/null || exit 1
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --csv --log-file gpurun_out/${TAG}_launches_bench_64spp.csv \
-  python bench.py --spp 64 --steps 1 --warmup 3 --no-parity --no-cpu-baseline > gpurun_out/${TAG}_ncu_launches.log 2>&1
+  python bench.py --spp 64 --steps 1 --warmup 3 --no-parity --no-cpu-baseline --no-secondary > gpurun_out/${TAG}_ncu_launches.log 2>&1
 python tools/prof_render.py c2 8 > gpurun_out/${TAG}_prof_plain.log 2>&1 || exit 1
 for k in k_extend k_connect; do
   timeout 600 ncu --set full --import-source on --clock-control none -k regex:$k -s 6 -c 1 -o gpurun_out/${TAG}_ncu_$k -f python tools/prof_render.py c2 8 > gpurun_out/${TAG}_ncu_$k.log 2>&1
