@@ -40,9 +40,6 @@ struct TravCounters { // only maintained by the COUNT instantiations
 #endif
 #define SPT_WSTASH (SPT_WORLD_STASH ? 5 : 0) // extra uint2 rows of the shared stack that hold the stashed world ray
 #define SPT_LSTACK 32       // overflow entries in local memory (untouched unless a ray goes deeper than SPT_SSTACK)
-#ifndef SPT_FETCH_STATIC
-#define SPT_FETCH_STATIC 0   // 1: chunks dealt round-robin to warps instead of a global atomic cursor
-#endif
 #ifndef SPT_TRAV_PREFETCH
 #define SPT_TRAV_PREFETCH 0 // prefetching the next child node after a node step: measured -7 % (C2), kept as a tuning knob
 #endif
@@ -429,11 +426,12 @@ SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCoun
   uint2 l_stack[SPT_LSTACK];
   TravStack st; st.sh = &s_stack[0][threadIdx.x]; st.lo = l_stack;
   const uint32_t total = src.total(), lane = threadIdx.x & 31u, FULL = 0xffffffffu;
-  uint32_t w_next = 0, w_end = 0, idx = 0;
-#if SPT_FETCH_STATIC
-  uint32_t chunk = blockIdx.x * (SPT_TRAV_BLOCK / 32) + (threadIdx.x >> 5);
-  (void)next;
-#endif
+  // The FIRST chunk of every warp is dealt statically by its index in the grid, further chunks come from the atomic cursor (which
+  // therefore starts behind the static ones).  A launch with little work — a draining pool — then needs no atomic at all, and warps
+  // beyond the work leave at once: 4736 warps hitting one address with atomicAdd was a ~50 us floor under every such launch.
+  const uint32_t n_warps = gridDim.x * (SPT_TRAV_BLOCK / 32), gwarp = blockIdx.x * (SPT_TRAV_BLOCK / 32) + (threadIdx.x >> 5);
+  const uint32_t static_end = n_warps * src.chunk();
+  uint32_t w_next = min(gwarp * src.chunk(), total), w_end = min(w_next + src.chunk(), total), idx = 0;
   bool exhausted = false, has = false;
   Trav T;
   T.ng = T.tg = make_uint2(0u, 0u); T.cur_inst = -1; T.sp = 0;
@@ -442,14 +440,12 @@ SPT_D void trace_persistent(const DScene& sc, Src& src, uint32_t* next, TravCoun
     const uint32_t idle = __ballot_sync(FULL, !has);
     if (idle == FULL || __popc(idle) >= SPT_FETCH_MIN_IDLE) {
       if (w_next >= w_end && !exhausted) { // next chunk of this warp
-#if SPT_FETCH_STATIC
-        const uint32_t base = chunk * src.chunk(); // chunks dealt round-robin over the warps of the grid: no atomics
-        chunk += gridDim.x * (SPT_TRAV_BLOCK / 32);
-#else
         uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(next, src.chunk());
-        base = __shfl_sync(FULL, base, 0);
-#endif
+        if (static_end >= total) base = total; // all the work was dealt statically
+        else {
+          if (lane == 0) base = atomicAdd(next, src.chunk()) + static_end;
+          base = __shfl_sync(FULL, base, 0);
+        }
         if (base >= total) exhausted = true;
         else { w_next = base; w_end = min(base + src.chunk(), total); }
       }
