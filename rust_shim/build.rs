@@ -25,4 +25,5 @@ fn main() {
     println!("cargo:rustc-link-search=native=/usr/local/cuda/lib64");
     println!("cargo:rustc-link-lib=cudart");
     println!("cargo:rustc-link-lib=stdc++");
+    println!("cargo:rustc-link-lib=dl"); // NCCL is dlopen()ed by the library (spt_comm_*), not linked
 }
