@@ -341,8 +341,9 @@ int32_t spt_render_device(SptScene* scene, const SptRenderDesc* desc, float* d_r
  * The rank join and the framebuffer exchange live behind this ABI, so a host binds ONE library: rank 0 calls spt_comm_unique_id and
  * hands the SPT_COMM_ID_BYTES bytes to the other ranks by whatever means it has (a file, a socket, MPI, a torch.distributed
  * broadcast), every rank calls spt_comm_create (ncclCommInitRank on its context's device; collective: all ranks must call it), and
- * then spt_render_gather per frame.  NCCL is loaded at run time (dlopen of libnccl.so.2); without it these calls return
- * SPT_ERR_UNSUPPORTED and everything else works.  The reference has no counterpart: it threads row bands in one process
+ * then spt_render_gather per frame.  NCCL is loaded at run time (dlopen of libnccl.so.2, or of the file SPT_NCCL_LIB names); without it
+ * these calls return SPT_ERR_UNSUPPORTED and everything else works.  A process holds ONE libnccl.so.2: a host that also uses another
+ * NCCL consumer with its own copy (PyTorch) must load that consumer before the first spt_comm_* call.  The reference has no counterpart: it threads row bands in one process
  * (renderer/pt.rs:243-261). */
 #define SPT_COMM_ID_BYTES 128
 typedef struct SptComm SptComm;

@@ -656,8 +656,12 @@ struct NcclApi {
 NcclApi g_nccl;
 int nccl_load() {
   if (g_nccl.lib) return SPT_OK;
+  // A process holds ONE libnccl.so.2 (the loader matches by soname): if the host also uses another NCCL consumer with its own copy
+  // (PyTorch bundles a newer one than the system's), that consumer must be loaded FIRST, or it will bind to whatever was loaded
+  // here and may miss symbols.  SPT_NCCL_LIB names the file to load instead of the default search.
   void* h = nullptr;
-  for (const char* name : {"libnccl.so.2", "libnccl.so"}) { h = dlopen(name, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
+  if (const char* e = getenv("SPT_NCCL_LIB")) h = dlopen(e, RTLD_NOW | RTLD_LOCAL);
+  for (const char* name : {"libnccl.so.2", "libnccl.so"}) { if (h) break; h = dlopen(name, RTLD_NOW | RTLD_LOCAL); }
   if (!h) return fail(SPT_ERR_UNSUPPORTED, std::string("spt_comm: cannot load libnccl.so.2 (") + dlerror() + ")");
   NcclApi a; a.lib = h;
   bool ok = true;

@@ -27,7 +27,17 @@ class Comm:
     """spt_comm_create: this process' rank in the library's NCCL communicator (one process per GPU).  `id_bytes`: the 128 bytes rank 0
     got from Comm.unique_id(), handed to every rank by the host (see Comm.from_torch)."""
 
+    @staticmethod
+    def _load_other_nccl_consumers_first():
+        """A process holds one libnccl.so.2.  PyTorch bundles its own (newer than the system's) and must bind to THAT one, so it has
+        to be loaded before the library dlopen()s libnccl.so.2 — else a later `import torch` fails on a missing symbol."""
+        try:
+            import torch  # noqa: F401
+        except ImportError:
+            pass
+
     def __init__(self, ctx, id_bytes, rank, world_size):
+        self._load_other_nccl_consumers_first()
         self.ctx, self.lib, self.rank, self.world_size = ctx, ctx.lib, rank, world_size
         buf = (C.c_uint8 * abi.COMM_ID_BYTES).from_buffer_copy(bytes(id_bytes))
         self.h = C.c_void_p()
@@ -35,6 +45,7 @@ class Comm:
 
     @staticmethod
     def unique_id(lib=None):
+        Comm._load_other_nccl_consumers_first()
         lib = lib or abi.load_library()
         buf = (C.c_uint8 * abi.COMM_ID_BYTES)()
         abi.check(lib, lib.spt_comm_unique_id(buf))
