@@ -263,6 +263,8 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
   hs.inst.resize(d.n_instances); hs.inst_shade.resize(d.n_instances);
   std::vector<Box3> inst_box(d.n_instances);
   std::vector<A3> inst_fwd(d.n_instances);
+  bool tlas_tight = true;
+  if (const char* e = getenv("SPT_TLAS_TIGHT")) tlas_tight = atoi(e) != 0;
   for (int i = 0; i < d.n_instances; i++) {
     const SptInstanceDesc& in = d.instances[i];
     if (in.surface < 0 || in.surface >= d.n_surfaces) return bad("instance: bad surface index");
@@ -288,6 +290,23 @@ std::string flatten_scene(const SptSceneDesc& d, HostScene& hs) {
       const V3 p = point(a, V3{(c & 4) ? pb.hi[0] : pb.lo[0], (c & 2) ? pb.hi[1] : pb.lo[1], (c & 1) ? pb.hi[2] : pb.lo[2]});
       wb.lo[0] = std::min(wb.lo[0], p.x); wb.lo[1] = std::min(wb.lo[1], p.y); wb.lo[2] = std::min(wb.lo[2], p.z);
       wb.hi[0] = std::max(wb.hi[0], p.x); wb.hi[1] = std::max(wb.hi[1], p.y); wb.hi[2] = std::max(wb.hi[2], p.z);
+    }
+    // The TLAS box only culls (hits come from the leaf tests), so it may be tighter than the reference's box of the transformed
+    // object box: for a rotated mesh instance the box of its transformed VERTICES (a hit point lies in their convex hull), padded
+    // outward by 1e-5 of its extent against rounding.  C5's bunnies, turned by arbitrary angles about y: fewer false instance visits.
+    if (tlas_tight && in.prim_kind == SPT_PRIM_TRIMESH && d.meshes[in.prim_index].n_verts <= (1 << 20) &&
+        (a.m.cx.y != 0.f || a.m.cx.z != 0.f || a.m.cy.x != 0.f || a.m.cy.z != 0.f || a.m.cz.x != 0.f || a.m.cz.y != 0.f)) {
+      const SptMeshDesc& m = d.meshes[in.prim_index];
+      Box3 tb; for (int k = 0; k < 3; k++) { tb.lo[k] = FLT_MAX; tb.hi[k] = -FLT_MAX; }
+      for (int v = 0; v < m.n_verts; v++) {
+        const V3 p = point(a, V3{m.position[3 * v], m.position[3 * v + 1], m.position[3 * v + 2]});
+        tb.lo[0] = std::min(tb.lo[0], p.x); tb.lo[1] = std::min(tb.lo[1], p.y); tb.lo[2] = std::min(tb.lo[2], p.z);
+        tb.hi[0] = std::max(tb.hi[0], p.x); tb.hi[1] = std::max(tb.hi[1], p.y); tb.hi[2] = std::max(tb.hi[2], p.z);
+      }
+      for (int k = 0; k < 3; k++) {
+        const float pad = 1e-5f * (tb.hi[k] - tb.lo[k]) + 1e-6f * std::max(std::fabs(tb.lo[k]), std::fabs(tb.hi[k]));
+        wb.lo[k] = std::max(wb.lo[k], tb.lo[k] - pad); wb.hi[k] = std::min(wb.hi[k], tb.hi[k] + pad); // never looser than the reference's box
+      }
     }
     inst_box[i] = wb; inst_fwd[i] = a;
     DInstanceShade sh;
