@@ -115,6 +115,7 @@ struct Sim {
   void node(Lane& L) {
     const uint32_t bit = bfind(L.ng.y), base = L.ng.x, imask = L.ng.y;
     L.ng.y &= ~(1u << bit);
+    if (L.tg.y != 0u) L.stack.push_back(L.tg); // eager mode only: leftover triangles wait on the stack
     if (L.ng.y > 0x00ffffffu) L.stack.push_back(L.ng);
     const uint32_t slot = (bit - 24u) ^ L.r.octinv;
     const uint32_t rel = (uint32_t)__builtin_popcount(imask & ~(0xffffffffu << slot));
@@ -190,7 +191,8 @@ struct SimCfg {
   int32_t tri_per_round;
   int32_t tri_dist;     // 1: the pending triangle tests of the whole warp are dealt to all 32 lanes (one or more passes per round)
   int32_t node_twice;   // 1: a second node stage at the end of the round for lanes that have a node pending and no leaf
-  int32_t inst_dist;    // reserved
+  int32_t inst_dist;    // EAGER node step: 1 = a lane with a node group pending takes its node step even when a triangle group is still pending
+                        // (the leftover triangles go on the stack and are tested after the new subtree)
   int32_t slots;        // ray slots per warp (32 = one ray per lane in registers; 64 / 96: ray state in shared memory, every stage
                         // compacts the slots that need it onto the 32 lanes, up to max_pass passes of 32 per round)
   int32_t max_pass;     // passes per stage and round in the slot design
@@ -272,7 +274,7 @@ int sim_run(void* scene, const SptRay* rays, int64_t n, const SimCfg* cfg, SimOu
         }
       };
       auto w_pop = [&](const Lane& L) { return !S.has_node(L) && !S.has_leaf(L); };
-      auto w_node = [&](const Lane& L) { return S.has_node(L) && !S.has_leaf(L); };
+      auto w_node = [&](const Lane& L) { return S.has_node(L) && (!S.has_leaf(L) || (cfg->inst_dist == 1 && L.cur_inst >= 0)); };
       auto w_inst = [&](const Lane& L) { return S.has_leaf(L) && L.cur_inst < 0; };
       auto w_tri = [&](const Lane& L) { return S.has_leaf(L) && L.cur_inst >= 0; };
       const int P = slot_design ? max_pass : 1;

@@ -86,14 +86,15 @@ def shadow_mix(fs, n, seed=3):
 
 BASE = dict(any=0, n_warps=48, chunk=64, min_idle=6, tri_per_round=2, tri_dist=0, node_twice=0, inst_dist=0, slots=32, max_pass=1, pop_end=0, order=0, gate_leaf=1, gate_wait=1, gate=1,
             c_round=45.0, c_pop=25.0, c_node=250.0, c_inst=110.0, c_tri=75.0, c_tri_dist=110.0, c_tri_setup=50.0, c_slot=30.0)
-VARIANTS = {
-    "round1": {},
-    "pop_end (now)": dict(pop_end=1),
-    "gate 8 wait 1": dict(pop_end=1, gate_leaf=8, gate_wait=1),
-    "gate 8 wait 2": dict(pop_end=1, gate_leaf=8, gate_wait=2),
-    "gate 12 wait 2": dict(pop_end=1, gate_leaf=12, gate_wait=2),
-    "gate 12 wait 3": dict(pop_end=1, gate_leaf=12, gate_wait=3),
-    "gate 16 wait 3": dict(pop_end=1, gate_leaf=16, gate_wait=3),
+VARIANTS = {  # the design space explored in round 2 (profiles/README.md has the GPU measurements of the ones that were built)
+    "round 1 (pop first)": {},
+    "now (pop last)": dict(pop_end=1),
+    "now, refill at 3 idle": dict(pop_end=1, min_idle=3),
+    "helper triangle pass": dict(tri_dist=2, pop_end=1, tri_per_round=1, c_tri_dist=100.0),      # built: -10 % on the GPU
+    "all pending triangles dealt to 32 lanes": dict(tri_dist=1, pop_end=1),
+    "eager node step": dict(pop_end=1, inst_dist=1),                                              # identical: leaves drain within the round
+    "leaf stages gated at 8 lanes": dict(pop_end=1, gate_leaf=8, gate_wait=1),
+    "64 ray slots per warp, stages gated at 16": dict(slots=64, min_idle=8, pop_end=1, max_pass=2, gate=16),  # not built (state through shared memory)
 }
 
 if __name__ == "__main__":
