@@ -17,6 +17,9 @@ struct ShadowRay { float3 o, d, c; float tmin, tmax; bool emit; };
 #ifndef SPT_SHADE_DEFER_SAMPLE
 #define SPT_SHADE_DEFER_SAMPLE 1
 #endif
+#ifndef SPT_PROBE_STAGED
+#define SPT_PROBE_STAGED 1 // 1: the BSSRDF probe is traced warp-synchronously in fixed-stage rounds (traverse_staged), 0: per-lane loop
+#endif
 #ifndef SPT_SHADE_PREFETCH
 #define SPT_SHADE_PREFETCH 0 // 0 off (default: measured neutral on C2/C3/C4), 1 prefetch.global.L2, 2 prefetch.global.L1
 #endif
@@ -183,7 +186,11 @@ __global__ void __launch_bounds__(SPT_BLOCK, ShadeCfg<MAT>::min_blocks) k_shade(
           n_probe++;
           uint2 l_stack[SPT_LSTACK];
           TravStack tst; tst.sh = &s_stack[0][threadIdx.x]; tst.lo = l_stack;
+#if SPT_PROBE_STAGED
+          ok = traverse_staged<false, COUNT>(__activemask(), sc, start, -sn, 1e-4f, ph, tc, tst); // the lanes that probe in this trip, together
+#else
           ok = traverse<false, COUNT>(sc, start, -sn, 1e-4f, ph, tc, tst);
+#endif
           if (ok) {
             HitGeom pg; load_hit(sc, start, -sn, ph, pg);
             const DSurface psf = sc.surfaces[pg.surface];

@@ -408,6 +408,29 @@ SPT_D bool traverse(const DScene& sc, float3 ow, float3 dw, float tmin, HitRec& 
   return hit.inst >= 0;
 }
 
+// The same single-ray query run WARP-SYNCHRONOUSLY by the lanes `m` that reach it together (the BSSRDF probe inside k_shade<7>): the
+// lanes advance in the fixed-stage rounds of the persistent driver below — node step, instance visit, triangle test x2, pop — instead of
+// drifting through the loops of traverse() one by one under independent thread scheduling (ncu round 1: 3.8 of 32 lanes in such loops).
+// Every lane of `m` must call it; a lane whose ray is finished idles until the last one is done.  Same hits as traverse().
+template <bool ANY, bool COUNT>
+SPT_D bool traverse_staged(unsigned m, const DScene& sc, float3 ow, float3 dw, float tmin, HitRec& hit, TravCounters& cnt, const TravStack& st) {
+  Trav T;
+  bool has = !sc.tlas_empty;
+  trav_begin(T, ow, dw, tmin, hit.t);
+  while (__any_sync(m, has)) {
+    bool fin = false;
+    if (has && trav_has_node(T) && !trav_has_leaf(T)) trav_node<COUNT>(sc, T, st, cnt);
+    if (has && trav_has_leaf(T) && T.cur_inst < 0) fin = trav_inst<ANY, COUNT>(sc, T, st, cnt);
+#pragma unroll
+    for (int k = 0; k < 2; k++)
+      if (has && !fin && trav_has_leaf(T) && T.cur_inst >= 0) fin = trav_tri<ANY, COUNT>(sc, T, cnt);
+    if (has && !fin && !trav_has_node(T) && !trav_has_leaf(T)) fin = trav_pop(T, st);
+    if (fin) has = false;
+  }
+  hit = T.hit;
+  return hit.inst >= 0;
+}
+
 // Persistent-warp driver.  Src provides
 //   uint32_t chunk() const;                                            candidates a warp reserves at a time (one atomic); warp-uniform
 //   uint32_t total() const;                                            number of candidate rays of this launch
