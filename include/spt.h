@@ -242,7 +242,9 @@ typedef struct SptRenderDesc { /* OutputConfig (renderer/mod.rs:9-14) + PathTrac
   float filter_radius;     /* box filter radius in pixels, filter/boxf.rs, in (0, 3.5].  0.5 = own-pixel mean.  Any other radius reproduces
                               Film::filter_pixel as written (film.rs:68-91, Q14): the UNWEIGHTED colour sum of every sample of the
                               (2R+1)^2 neighbour pixels, R = ceil(radius - 0.5), divided by the number of those samples that lie inside the
-                              box — brighter than a mean for every radius but 0.5; a pixel with no sample in the box is inf / NaN */
+                              box — brighter than a mean for every radius but 0.5; a pixel with no sample in the box is inf / NaN.
+                              The sample offsets are recomputed from (seed, sampler, pixel, sample index), not stored: progressive passes
+                              that end in a radius != 0.5 must cover consecutive sample ranges with the SAME seed and sampler */
   uint64_t seed;           /* RNG key; the stream of a path depends only on (seed, pixel, sample) */
   int32_t tile_w, tile_h;  /* screen tile size for rank interleaving (0 = SPT_DEFAULT_TILE_W x _H); multiples of 8 / 4 */
   int32_t rank, world_size;/* this process renders the tiles it owns; others stay 0 */
@@ -355,7 +357,8 @@ int32_t spt_comm_destroy(SptComm* comm);
  * over NVLink — to `root`, which unpacks them into its film and reconstructs the frame into d_rgb_mean (DEVICE memory,
  * width*height*3 f32; ignored on the other ranks, may be NULL there).  Because the film is integer the result is bit-identical to the
  * one-GPU frame for every filter radius.  stats (may be NULL) are this rank's; seconds_stage[5] = device time of exchange + resolve.
- * Collective: every rank must call it with the same desc. */
+ * Collective: every rank must call it with the same desc; a rank that fails before the exchange (e.g. out of memory) leaves the others
+ * waiting in NCCL, as with any collective. */
 int32_t spt_render_gather(SptScene* scene, SptComm* comm, const SptRenderDesc* desc, int32_t root, float* d_rgb_mean, SptStats* stats);
 
 /* Progressive dump / resume: the film is 3 x int64 per pixel (sums in 2^-24 fixed point), row 0 = top.  spt_film_save copies the
