@@ -382,3 +382,45 @@ def test_henyey_greenstein_normalised_and_invertible(g):
         assert abs(c64.mean() - g64) < 2e-3                                                     # mean sampled cosine = +g
         mean_phase_cos = 2 * math.pi * np.trapezoid(p.astype(np.float64) * c.astype(np.float64), c.astype(np.float64))
         assert abs(mean_phase_cos - (-g64)) < 2e-3                                              # mean cosine of the evaluated phase = -g
+
+
+def test_conductor_fresnel_at_normal_incidence_and_mirror_direction():
+    """SpecularConductor::sample (specular_conductor.rs:19-36): wi = reflect(wo) = (-x, -y, z), bxdf = F / |cos|, pdf = 1, with the
+    exact conductor Fresnel (bxdf/util.rs:87-112).  At normal incidence F = ((n-1)^2 + k^2) / ((n+1)^2 + k^2) per channel — textbook value,
+    worked here for n = (0.2, 0.9, 1.1), k = (3.9, 2.4, 2.2): (0.95195, 0.61580, 0.52432)."""
+    sc = orc.OracleScene(material_scene(MATS["conductor_smooth"][0]))
+    s = sc.bxdf(_queries([0, 0, 1], [[0, 0, 1]]))[0]
+    n, k = np.array([0.2, 0.9, 1.1]), np.array([3.9, 2.4, 2.2])
+    want = ((n - 1) ** 2 + k ** 2) / ((n + 1) ** 2 + k ** 2)
+    assert np.allclose(want, [0.95195, 0.61580, 0.52432], atol=2e-5)
+    assert np.allclose(list(s.sample_f), want, rtol=2e-5) and s.sample_pdf == 1.0 and s.is_delta == 1
+    assert np.allclose(list(s.sample_wi), [0, 0, 1], atol=1e-7) and s.sample_lobe == 2 and s.sample_dir == 0
+    wo = np.array([0.6, 0.0, 0.8])
+    s = sc.bxdf(_queries(wo, [[-0.6, 0.0, 0.8]]))[0]
+    assert np.allclose(list(s.sample_wi), [-0.6, 0.0, 0.8], atol=1e-6)
+    assert np.allclose(list(s.eval_f), list(s.sample_f), rtol=1e-5)      # bxdf(wo, reflect(wo)) returns the same F / |cos| (:41-49)
+    assert (np.array(list(s.sample_f)) * 0.8 <= 1.0 + 1e-5).all()         # F <= 1
+
+
+def test_dielectric_refraction_follows_snell():
+    """SpecularDielectric::sample, transmission branch (specular_dielectric.rs:40-58) with util::refract: for wo at 60 degrees from the
+    normal outside glass of ior 1.5, sin(theta_t) = sin(60) / 1.5 = 0.57735, cos(theta_t) = 0.81650; wi lies in the plane of incidence on
+    the other side: wi = (-0.57735, 0, -0.81650).  Fresnel for unpolarised light at 60 degrees: Rs = 0.17656, Rp = 0.00180,
+    F = 0.08919; the draw 0.5 >= F selects transmission with pdf 1 - F and bxdf = (1/1.5)^2 (1 - F) / |cos(theta_t)|."""
+    sc = orc.OracleScene(material_scene(MATS["dielectric_smooth"][0]))
+    si, ci = math.sin(math.radians(60)), math.cos(math.radians(60))
+    st = si / 1.5
+    ct = math.sqrt(1 - st * st)
+    rs = ((ci - 1.5 * ct) / (ci + 1.5 * ct)) ** 2
+    rp = ((1.5 * ci - ct) / (1.5 * ci + ct)) ** 2
+    F = 0.5 * (rs + rp)
+    assert abs(st - 0.57735) < 1e-5 and abs(ct - 0.81650) < 1e-5 and abs(F - 0.08919) < 2e-5
+    s = sc.bxdf(_queries([si, 0, ci], [[0, 0, 1]], [0.5] * 8))[0]
+    assert s.sample_dir == 1 and np.allclose(list(s.sample_wi), [-st, 0.0, -ct], atol=2e-6)
+    assert abs(s.sample_pdf - (1 - F)) < 2e-5
+    assert np.allclose(list(s.sample_f), [(1 - F) / 2.25 / ct] * 3, rtol=5e-5)
+    r = sc.bxdf(_queries([si, 0, ci], [[0, 0, 1]], [0.01] * 8))[0]        # the draw 0.01 < F selects reflection
+    assert r.sample_dir == 0 and np.allclose(list(r.sample_wi), [-si, 0.0, ci], atol=2e-6) and abs(r.sample_pdf - F) < 2e-5
+    # from inside at 60 degrees: sin = 0.866 * 1.5 > 1 -> total internal reflection: F = 1, reflection whatever the draw
+    t = sc.bxdf(_queries([si, 0, -ci], [[0, 0, 1]], [0.999] * 8))[0]
+    assert t.sample_dir == 0 and abs(t.sample_pdf - 1.0) < 1e-6 and np.allclose(list(t.sample_wi), [-si, 0.0, -ci], atol=2e-6)
