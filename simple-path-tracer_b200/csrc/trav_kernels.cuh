@@ -3,6 +3,14 @@
 #include "wavefront.cuh"
 
 #define SPT_BLOCK SPT_TRAV_BLOCK
+#ifndef SPT_PF_L1
+#define SPT_PF_L1 0
+#endif
+#if SPT_PF_L1
+#define SPT_PF_INSTR "prefetch.global.L1 [%0];"
+#else
+#define SPT_PF_INSTR "prefetch.global.L2 [%0];"
+#endif
 
 SPT_D void flush_trav_counters(DevCounters* ctr, const TravCounters& tc) {
   warp_sum_to(&ctr->nodes, tc.nodes); warp_sum_to(&ctr->tris, tc.tris); warp_sum_to(&ctr->insts, tc.insts);
@@ -20,6 +28,7 @@ struct ExtendSrc { // every live path of the pool: closest hit (pt.rs:49-50)
   SPT_D uint32_t chunk() const { return chunk_; }
   SPT_D uint32_t total() const { return n_list ? n_list : (uint32_t)P.pool.n; }
   SPT_D uint32_t slot_of(uint32_t i) const { return n_list ? P.ext_queue[i] : i; }
+  SPT_D void prefetch(uint32_t i) const { if (!n_list) { asm volatile(SPT_PF_INSTR ::"l"(P.pool.rec + i)); if ((i & 7u) == 0u) asm volatile("prefetch.global.L2 [%0];" ::"l"(P.pool.flags + i)); } }
   SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
     const uint32_t s = slot_of(i);
     if (!(P.pool.flags[s] & 1u)) return false;
@@ -40,6 +49,7 @@ struct ConnectSrc { // the queued shadow rays: any hit (pt.rs:81, :169); unocclu
   uint32_t chunk_;
   SPT_D uint32_t chunk() const { return chunk_; }
   SPT_D uint32_t total() const { return n; }
+  SPT_D void prefetch(uint32_t i) const { if ((i & 1u) == 0u) { asm volatile("prefetch.global.L2 [%0];" ::"l"(P.sq.o + i)); asm volatile("prefetch.global.L2 [%0];" ::"l"(P.sq.d + i)); } }
   SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
     const float4 o4 = P.sq.o[i], d4 = P.sq.d[i];
     o = mk3(o4); d = mk3(d4); tmin = o4.w; tmax = d4.w;
@@ -101,6 +111,7 @@ struct BatchSrc {
   HitIO* __restrict__ hits;       // closest-hit output or null
   uint8_t* __restrict__ occ;      // any-hit output or null
   SPT_D uint32_t chunk() const { return SPT_FETCH_CHUNK; }
+  SPT_D void prefetch(uint32_t i) const { asm volatile("prefetch.global.L2 [%0];" ::"l"(rays + 2 * (size_t)i)); }
   SPT_D uint32_t total() const { return n; }
   SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
     const float4 a = ldg4(rays + 2 * (size_t)i), b = ldg4(rays + 2 * (size_t)i + 1);
