@@ -8,6 +8,9 @@
 #include <algorithm>
 #include <new>
 #include <cmath>
+#include <mutex>
+#include <dlfcn.h>
+#include <nccl.h> // types and enums only: the functions are bound at run time (nccl_load)
 #include "../../include/spt.h"
 #include "flatten.h"
 #include "launch.h"
@@ -639,8 +642,6 @@ extern "C" int32_t spt_render_device(SptScene* s, const SptRenderDesc* r, float*
 // ---- multi-GPU: the rank join and the framebuffer exchange behind the C ABI -------------------------------------------------------------
 // NCCL is bound at run time (dlopen of libnccl.so.2: the copy a host such as PyTorch has already loaded, else the system one), so the
 // library has no link-time dependency on it and single-GPU hosts never touch it.
-#include <dlfcn.h>
-#include <nccl.h>
 namespace {
 struct NcclApi {
   void* lib = nullptr;
@@ -654,7 +655,9 @@ struct NcclApi {
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
 };
 NcclApi g_nccl;
+std::mutex g_nccl_mutex;
 int nccl_load() {
+  std::lock_guard<std::mutex> lock(g_nccl_mutex); // two hosts threads may make their first spt_comm_* call at once
   if (g_nccl.lib) return SPT_OK;
   // A process holds ONE libnccl.so.2 (the loader matches by soname): if the host also uses another NCCL consumer with its own copy
   // (PyTorch bundles a newer one than the system's), that consumer must be loaded FIRST, or it will bind to whatever was loaded
