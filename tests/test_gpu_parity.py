@@ -331,6 +331,50 @@ def test_textured_scene_matches_oracle(ctx):
     sc.close()
 
 
+def test_empty_scene_and_degenerate_triangles(ctx, tmp_path):
+    """Edge cases of the domain: (a) a scene without any instance (empty aggregate: every ray misses, bvh.rs:238-283 on an empty tree) under an
+    environment — the frame is the environment seen by the camera; (b) a mesh holding zero-area triangles (two coincident vertices, three collinear
+    ones) and a sliver next to regular ones: Triangle::intersect_ray rejects det == 0 only (triangle.rs:131), everything else must agree with the oracle."""
+    import orc
+    from spt import core, loader, scenes
+    d = scenes.c3()
+    d["instances"] = []
+    fs = loader.load_scene(d, scenes.BASE_PATH)
+    sc, osc = core.Scene(ctx, fs), orc.OracleScene(fs)
+    r = R.primary_rays(fs, 64, 36)
+    h = sc.trace(r)
+    assert (h["inst_id"] == -1).all() and np.array_equal(h["t"], r["t_max"]) and (sc.occluded(r) == 0).all()
+    gi, gst = sc.render(64, 36, spp=4, seed=3)
+    oi, ost = osc.render(64, 36, spp=4, seed=3, rng_mode=1)
+    assert gst["paths"] == ost["paths"] and gst["shadow_rays"] == 0 and gst["ext_rays"] == gst["paths"]
+    assert np.allclose(gi, oi, rtol=2e-3, atol=1e-5) and gi.mean() > 0
+    sc.close()
+    pos = np.array([[-1, 0, -1], [1, 0, -1], [1, 0, 1], [-1, 0, 1],            # a regular quad ...
+                    [0, 0.5, 0], [0, 0.5, 0], [1, 0.5, 0],                        # ... a triangle with two coincident vertices
+                    [-1, 0.7, 0], [0, 0.7, 0], [1, 0.7, 0],                       # ... three collinear vertices
+                    [-1, 0.9, -1], [1, 0.9, -1], [1, 0.9 + 1e-7, -1 + 1e-6]], np.float32)   # ... and a sliver
+    idx = np.array([[0, 1, 2], [0, 2, 3], [4, 5, 6], [7, 8, 9], [10, 11, 12]], np.uint32)
+    np.savez(tmp_path / "degenerate.npz", positions=pos, indices=idx)
+    d = scenes.c1b()
+    d["primitives"] = d["primitives"] + [{"type": "trimesh", "name": "deg", "obj_file": str(tmp_path / "degenerate.npz")}]
+    d["instances"][1] = {"name": "floor", "primitive": "deg", "material": "lambert_blue", "translate": [0.0, -1.0, 0.0], "scale": [5.0, 1.0, 5.0]}
+    fs = loader.load_scene(d, scenes.BASE_PATH)
+    sc, osc = core.Scene(ctx, fs), orc.OracleScene(fs, fix_q1=True)
+    for rays in (R.primary_rays(fs, 256, 144), R.incoherent_rays(fs, 1 << 16)):
+        _assert_hits(R.compare_hits(osc.trace(rays)[0], sc.trace(rays)))
+    down = np.zeros(5, R.RAY_DT)                                                  # straight down through each degenerate triangle's "interior"
+    down["origin"] = [[0.5 * 5, 3, 0], [0, 3, 0], [2.5, 3, 0], [0.1, 3, 0.2], [4.9, 3, -4.999]]
+    down["direction"] = [0, -1, 0]; down["t_min"] = 1e-4; down["t_max"] = R.FMAX
+    a, b = osc.trace(down)[0], sc.trace(down)
+    assert np.array_equal(a["prim_id"], b["prim_id"]) and np.array_equal(a["t"], b["t"])
+    fr = R.incoherent_rays(fs, 1 << 14, finite_tmax=True)
+    assert (osc.occluded(fr) == sc.occluded(fr)).mean() >= 0.9999
+    gi, _ = sc.render(96, 64, spp=4, seed=2)
+    oi, _ = osc.render(96, 64, spp=4, seed=2, rng_mode=1)
+    _assert_paired_images("c1b", gi, oi, 0.99)
+    sc.close()
+
+
 def test_delta_lights_and_spot(ctx):
     import orc
     from spt import core, loader, scenes
