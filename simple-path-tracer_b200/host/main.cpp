@@ -7,7 +7,7 @@
 //   --base-path P       resolve relative obj_file / image_file / external JSON against P instead of the scene file
 //   --device N  --seed N  --pool N  --spp N (overrides the renderer file)
 //   --gpus N            one process per GPU: forks N ranks (GPU r = rank r) that render interleaved tiles and gather the
-//                       frame on rank 0 with one ncclReduce; rank 0 writes the image
+//                       frame on rank 0 with spt_render_gather (owned tiles only, over NCCL inside the library); rank 0 writes the image
 //   --rank R --world-size W [--nccl-id FILE]   what --gpus passes to each rank; without --nccl-id the rank only renders
 //                       the tiles it owns (no gather)
 //   --frames N          render the frame N times (same seed) and report the last one: steady-state timing without the

@@ -7,7 +7,7 @@
 CPU integrator — is not part of this product and is rejected (there is no CPU fallback).
 
 Multi-GPU (one process per GPU): when torch.distributed is initialised, each rank renders its interleaved tiles with
-the scene replicated, and the framebuffer is summed onto rank 0 with one NCCL reduce (disjoint tiles: exact).
+the scene replicated, and the owned tiles of every rank are gathered on rank 0 inside the library (spt_render_gather: integer film over NCCL).
 """
 from dataclasses import dataclass
 from typing import Optional
