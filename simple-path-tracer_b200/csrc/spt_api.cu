@@ -402,13 +402,17 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   // pool-fills spends its time filling and draining the pool and wants a small one: the measured optimum is a pool that
   // finishes the render in ~20 iterations.  How many samples an iteration starts depends on how long the scene's paths
   // live, which the first iterations tell: the render starts on samples/16 slots (right for C1, whose paths mostly end at
-  // their first hit) and, after three iterations, widens the ACTIVE part of the pool up to the allocated samples/8.
+  // their first hit) and, after three iterations, widens the ACTIVE part of the pool up to the allocated samples/4 (aiming at ~10 iterations).
   // 2^24 slots = 2.95 GB.
   const unsigned long long all_samples = (unsigned long long)n_px * (unsigned long long)spp_pass;
   const unsigned long long pool_lo = std::min<unsigned long long>(1ull << 22, std::max<unsigned long long>(1ull << 16, all_samples));
   const unsigned long long rank_samples = all_samples / (unsigned long long)world;
   auto round_pool = [](unsigned long long n) { return (int)std::max<unsigned long long>(SPT_TRAV_BLOCK, (n + SPT_TRAV_BLOCK - 1) / SPT_TRAV_BLOCK * SPT_TRAV_BLOCK); };
-  int pool_n = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 24, std::max<unsigned long long>(pool_lo, rank_samples / 8ull)); // allocated
+  // SPT_POOL_CAP_DIV / SPT_POOL_ITERS: the two constants of the rule (allocated = samples / cap_div; widening aims at `iters` iterations), for sweeps
+  unsigned long long cap_div = 4ull; double want_iters = 10.0; // re-tuned in round 2 (8 / 20 before): the kernels got 25 % faster, the per-iteration tails did not
+  if (const char* e = getenv("SPT_POOL_CAP_DIV")) cap_div = std::max(1, atoi(e));
+  if (const char* e = getenv("SPT_POOL_ITERS")) want_iters = std::max(1.0, atof(e));
+  int pool_n = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 24, std::max<unsigned long long>(pool_lo, rank_samples / cap_div)); // allocated
   int pool_start = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 24, std::max<unsigned long long>(pool_lo, rank_samples / 16ull)); // active at first
   pool_n = round_pool(pool_n); pool_start = std::min(pool_n, round_pool(pool_start));
   const size_t per_slot = sizeof(PathRec) + sizeof(float4) + 3 * sizeof(float4) + sizeof(int32_t) + sizeof(uint32_t) + (SPT_NQ + 1) * sizeof(uint32_t);
@@ -568,7 +572,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
         widen = false;
         const double per_slot_iter = (double)(s->h_ctr->cursor - cursor_1) / (2.0 * (double)P.pool.n);
         if (per_slot_iter > 0 && s->h_ctr->cursor < P.total_samples) {
-          const double want = (double)P.total_samples / (20.0 * per_slot_iter);
+          const double want = (double)P.total_samples / (want_iters * per_slot_iter);
           set_active_pool(std::min(pool_n, std::max(P.pool.n, round_pool((unsigned long long)want))));
         }
       }
