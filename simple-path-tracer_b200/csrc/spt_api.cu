@@ -401,7 +401,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   // want a big pool (C2..C5 at full length: 2^23 +5 %, 2^24 +7..10 % over 2^22; profiles/README.md), while a render of a few
   // pool-fills spends its time filling and draining the pool and wants a small one: the measured optimum is a pool that
   // finishes the render in ~20 iterations.  How many samples an iteration starts depends on how long the scene's paths
-  // live, which the first iterations tell: the render starts on samples/16 slots (right for C1, whose paths mostly end at
+  // live, which the first iterations tell: the render starts on samples/6 slots (samples/16 in round 1, right for C1 then, whose paths mostly end at
   // their first hit) and, after three iterations, widens the ACTIVE part of the pool up to the allocated samples/4 (aiming at ~10 iterations).
   // 2^24 slots = 2.95 GB.
   const unsigned long long all_samples = (unsigned long long)n_px * (unsigned long long)spp_pass;
@@ -412,8 +412,10 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   unsigned long long cap_div = 4ull; double want_iters = 10.0; // re-tuned in round 2 (8 / 20 before): the kernels got 25 % faster, the per-iteration tails did not
   if (const char* e = getenv("SPT_POOL_CAP_DIV")) cap_div = std::max(1, atoi(e));
   if (const char* e = getenv("SPT_POOL_ITERS")) want_iters = std::max(1.0, atof(e));
+  unsigned long long start_div = 6ull; // 16 in round 1; 6 measured best on renders of 60-130 M samples (C3 +2.8 %, C4 +2.2 %, C5 +1.7 %, C1 +0.8 %, C2 0 %)
+  if (const char* e = getenv("SPT_POOL_START_DIV")) start_div = std::max(1, atoi(e));
   int pool_n = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 24, std::max<unsigned long long>(pool_lo, rank_samples / cap_div)); // allocated
-  int pool_start = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 24, std::max<unsigned long long>(pool_lo, rank_samples / 16ull)); // active at first
+  int pool_start = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 24, std::max<unsigned long long>(pool_lo, rank_samples / start_div)); // active at first
   pool_n = round_pool(pool_n); pool_start = std::min(pool_n, round_pool(pool_start));
   const size_t per_slot = sizeof(PathRec) + sizeof(float4) + 3 * sizeof(float4) + sizeof(int32_t) + sizeof(uint32_t) + (SPT_NQ + 1) * sizeof(uint32_t);
   if (s->pool_n != pool_n) {
