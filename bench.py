@@ -346,11 +346,11 @@ def main():
                   "what": "algorithmic node + triangle + instance bytes per ray x rays/s of k_extend (requests that hit L1 never reach L2)"}
     except OSError:
         pass
-    # the library's default (spt_api.cu): samples/6 per rank within [2^22, 2^24] at first, widened after three iterations to
+    # the library's default (spt_api.cu): samples/6 per rank within [2^22, 2^25] at first, widened after three iterations to
     # what finishes the render in ~10 iterations, at most samples/4 (allocated)
     pool_lo = min(1 << 22, max(1 << 16, w * h * spp))
-    pool_slots = args.pool or min(1 << 24, max(pool_lo, w * h * spp // world // 6))
-    pool_alloc = args.pool or min(1 << 24, max(pool_lo, w * h * spp // world // 4))
+    pool_slots = args.pool or min(1 << 25, max(pool_lo, w * h * spp // world // 6))
+    pool_alloc = args.pool or min(1 << 25, max(pool_lo, w * h * spp // world // 4))
     roofline = {"bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                 "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": peak_src,
                 "bytes_per_ray": b_ray, "nodes_per_ray": n_node, "tris_per_ray": n_tri, "insts_per_ray": n_inst,

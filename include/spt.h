@@ -249,7 +249,7 @@ typedef struct SptRenderDesc { /* OutputConfig (renderer/mod.rs:9-14) + PathTrac
   int32_t tile_w, tile_h;  /* screen tile size for rank interleaving (0 = SPT_DEFAULT_TILE_W x _H); multiples of 8 / 4 */
   int32_t rank, world_size;/* this process renders the tiles it owns; others stay 0 */
   int32_t pool_size;       /* resident path slots, 180 B each (0 = default: 1/6 of this rank's camera samples at first, widened after three iterations to
-                              what ends the render in ~10 iterations — at most 1/4 of the samples — all kept within [2^22, 2^24];
+                              what ends the render in ~10 iterations — at most 1/4 of the samples — all kept within [2^22, 2^25];
                               fewer for renders of less than 2^22 samples, halved if the device is short of memory) */
   uint32_t flags;
   int32_t spp_first, spp_count; /* render only the samples [spp_first, spp_first + spp_count) of every pixel's spp (0, 0 = all).

@@ -396,14 +396,15 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   cudaStream_t st = s->stream;
   const size_t n_px = (size_t)r->width * r->height;
   // ---- buffers
-  // default pool: sized to this rank's camera samples, between 2^22 and 2^24 slots (fewer for renders smaller than 2^22 samples).
+  // default pool: sized to this rank's camera samples, between 2^22 and 2^25 slots (fewer for renders smaller than 2^22 samples).
   // Every iteration of the wavefront loop pays ~110 us of kernel tails and launch gaps whatever the pool holds, so long renders
   // want a big pool (C2..C5 at full length: 2^23 +5 %, 2^24 +7..10 % over 2^22; profiles/README.md), while a render of a few
   // pool-fills spends its time filling and draining the pool and wants a small one: the measured optimum is a pool that
   // finishes the render in ~20 iterations.  How many samples an iteration starts depends on how long the scene's paths
   // live, which the first iterations tell: the render starts on samples/6 slots (samples/16 in round 1, right for C1 then, whose paths mostly end at
   // their first hit) and, after three iterations, widens the ACTIVE part of the pool up to the allocated samples/4 (aiming at ~10 iterations).
-  // 2^24 slots = 2.95 GB.
+  // 2^25 slots = 6.0 GB (the cap was 2^24 in round 1, when 2^25 gained 0.6 %; with the faster kernels of round 2 it gains 1.0 % on C2 and
+  // 1.6 % on C3, 2^26 nothing more; 6 GB of a 180 GB device).  SPT_POOL_CAP_LOG2 overrides it.
   const unsigned long long all_samples = (unsigned long long)n_px * (unsigned long long)spp_pass;
   const unsigned long long pool_lo = std::min<unsigned long long>(1ull << 22, std::max<unsigned long long>(1ull << 16, all_samples));
   const unsigned long long rank_samples = all_samples / (unsigned long long)world;
@@ -414,8 +415,10 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   if (const char* e = getenv("SPT_POOL_ITERS")) want_iters = std::max(1.0, atof(e));
   unsigned long long start_div = 6ull; // 16 in round 1; 6 measured best on renders of 60-130 M samples (C3 +2.8 %, C4 +2.2 %, C5 +1.7 %, C1 +0.8 %, C2 0 %)
   if (const char* e = getenv("SPT_POOL_START_DIV")) start_div = std::max(1, atoi(e));
-  int pool_n = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 24, std::max<unsigned long long>(pool_lo, rank_samples / cap_div)); // allocated
-  int pool_start = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(1ull << 24, std::max<unsigned long long>(pool_lo, rank_samples / start_div)); // active at first
+  unsigned long long pool_cap = 1ull << 25;
+  if (const char* e = getenv("SPT_POOL_CAP_LOG2")) pool_cap = 1ull << std::min(28, std::max(16, atoi(e)));
+  int pool_n = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(pool_cap, std::max<unsigned long long>(pool_lo, rank_samples / cap_div)); // allocated
+  int pool_start = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(pool_cap, std::max<unsigned long long>(pool_lo, rank_samples / start_div)); // active at first
   pool_n = round_pool(pool_n); pool_start = std::min(pool_n, round_pool(pool_start));
   const size_t per_slot = sizeof(PathRec) + sizeof(float4) + 3 * sizeof(float4) + sizeof(int32_t) + sizeof(uint32_t) + (SPT_NQ + 1) * sizeof(uint32_t);
   if (s->pool_n != pool_n) {
