@@ -373,7 +373,7 @@ def main():
         "config": {"workload": f"{args.workload}: {w}x{h} @ {spp} spp, max_depth 8, recurrence sampler, box r=0.5",
                    "scene": "bunny_5k x3 (conductor, pbr_metallic iso+aniso) + room + emissive quad, power_is MIS" if args.workload == "c2" else args.workload,
                    "parallelism": f"tiles{world}", "pool_slots": pool_slots, "pool_slots_allocated": pool_alloc,
-                   "l2_policy": "per-step working set (path pool %d MB + film %d MB) exceeds the 126 MB L2; no explicit flush" % (pool_alloc * 180 >> 20, w * h * 24 >> 20)},
+                   "l2_policy": "per-step working set (path pool %d MB + film %d MB) exceeds the 126 MB L2; no explicit flush" % (pool_alloc * 184 >> 20, w * h * 24 >> 20)},
         "mrays_per_s": mrays, "rays_per_path": (ext + shadow + probe) / paths,
         "shadow_rays_culled_per_path": sum(s["shadow_culled"] for s in stats) / max(1.0, sum(s["paths"] for s in stats)),
         "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(w * h * 3 * 4)},

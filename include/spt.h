@@ -248,7 +248,7 @@ typedef struct SptRenderDesc { /* OutputConfig (renderer/mod.rs:9-14) + PathTrac
   uint64_t seed;           /* RNG key; the stream of a path depends only on (seed, pixel, sample) */
   int32_t tile_w, tile_h;  /* screen tile size for rank interleaving (0 = SPT_DEFAULT_TILE_W x _H); multiples of 8 / 4 */
   int32_t rank, world_size;/* this process renders the tiles it owns; others stay 0 */
-  int32_t pool_size;       /* resident path slots, 180 B each (0 = default: 1/6 of this rank's camera samples at first, widened after three iterations to
+  int32_t pool_size;       /* resident path slots, 184 B each (0 = default: 1/6 of this rank's camera samples at first, widened after three iterations to
                               what ends the render in ~10 iterations — at most 1/4 of the samples — all kept within [2^22, 2^25];
                               fewer for renders of less than 2^22 samples, halved if the device is short of memory) */
   uint32_t flags;

@@ -10,14 +10,23 @@
 __global__ void __launch_bounds__(SPT_LOGIC_BLOCK) k_logic(const DScene sc, const RenderParams P) {
   __shared__ uint32_t s_cnt[SPT_NQ], s_base[SPT_NQ];
   if (threadIdx.x < SPT_NQ) s_cnt[threadIdx.x] = 0;
+  const int par = P.parity;
+  // A draining pool: the previous iteration's generate left the list of the slots that are still alive (ext_queue[par ^ 1]) — this pass
+  // walks that list instead of the whole pool (a 16 M-slot pool holding 3 K paths cost 77 us here, in every one of the last iterations)
+  const bool from_list = P.ctr->it.list_valid[par ^ 1] != 0u;
+  const uint32_t n_prev = P.ctr->it.n_ext[par ^ 1];
   if (blockIdx.x == 0 && threadIdx.x == 0) { // connect + extend of the last iteration are done
-    P.ctr->it.live = 0; P.ctr->it.next_ext = 0; P.ctr->it.sq = 0; P.ctr->it.next_con = 0; P.ctr->it.n_ext = 0;
+    P.ctr->it.live = 0; P.ctr->it.next_ext = 0; P.ctr->it.sq = 0; P.ctr->it.next_con = 0; P.ctr->it.n_ext[par] = 0;
     P.ctr->it.drain = (P.use_ext_queue && P.ctr->cursor >= P.total_samples) ? 1u : 0u; // the cursor only moves in generate: one value for the whole iteration
   }
+  if (from_list && blockIdx.x > 0 && (uint32_t)(blockIdx.x * blockDim.x) >= n_prev) return; // whole block beyond the list
   __syncthreads();
-  const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+  int slot = -1;
+  if (from_list) { if (gid < n_prev) slot = (int)P.ext_queue[par ^ 1][gid]; }
+  else if (gid < (uint32_t)P.pool.n) slot = (int)gid;
   int cls = -1; uint32_t rank = 0;
-  if (slot < P.pool.n) {
+  if (slot >= 0) {
     const uint32_t flags = P.pool.flags[slot];
     if (flags & 1u) {
       const int inst = P.pool.hit_inst[slot];
@@ -132,24 +141,33 @@ __global__ void __launch_bounds__(SPT_LOGIC_BLOCK) k_generate(const DScene sc, c
     // Every camera sample has been started: nothing to regenerate.  The pool now empties within max_depth iterations, and a kernel
     // that scans it finds fewer and fewer rays per chunk (at 10 % live a lane of k_extend spends 9 rounds finding a ray that lives 4).
     // So this pass compacts the live slots into ext_queue (one atomic per block and trip) and k_extend fetches from that list.
-    for (int base_slot = blockIdx.x * blockDim.x; base_slot < P.pool.n; base_slot += gridDim.x * blockDim.x) {
-      const int slot = base_slot + (int)threadIdx.x;
-      const bool live = slot < P.pool.n && (P.pool.flags[slot] & 1u);
+    // From the second drain iteration on, the candidates are the previous iteration's list, not the pool.
+    const int par = P.parity;
+    const bool from_list = P.ctr->it.list_valid[par ^ 1] != 0u;
+    const uint32_t n_src = from_list ? P.ctr->it.n_ext[par ^ 1] : (uint32_t)P.pool.n;
+    const uint32_t* src = P.ext_queue[par ^ 1];
+    uint32_t* dst = P.ext_queue[par];
+    if (blockIdx.x == 0 && threadIdx.x == 0) P.ctr->it.list_valid[par] = 1u; // read by the NEXT iteration's kernels only
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n_src; base += gridDim.x * blockDim.x) {
+      const uint32_t idx = base + threadIdx.x;
+      const uint32_t slot = idx < n_src ? (from_list ? src[idx] : idx) : 0u;
+      const bool live = idx < n_src && (P.pool.flags[slot] & 1u);
       const uint32_t m = __ballot_sync(0xffffffffu, live);
       if (lane == 0) s_warp[warp] = __popc(m);
       __syncthreads();
       if (threadIdx.x == 0) {
         uint32_t total = 0;
         for (int w = 0; w < SPT_LOGIC_BLOCK / 32; w++) { const uint32_t c = s_warp[w]; s_warp[w] = total; total += c; }
-        s_base = total ? (unsigned long long)atomicAdd(&P.ctr->it.n_ext, total) : 0ull;
+        s_base = total ? (unsigned long long)atomicAdd(&P.ctr->it.n_ext[par], total) : 0ull;
       }
       __syncthreads();
-      if (live) { P.ext_queue[(uint32_t)s_base + s_warp[warp] + __popc(m & ((1u << lane) - 1u))] = (uint32_t)slot; n_live++; }
+      if (live) { dst[(uint32_t)s_base + s_warp[warp] + __popc(m & ((1u << lane) - 1u))] = slot; n_live++; }
       __syncthreads();
     }
     warp_sum_to32(&P.ctr->it.live, n_live);
     return;
   }
+  if (blockIdx.x == 0 && threadIdx.x == 0) P.ctr->it.list_valid[P.parity] = 0u; // no list from this iteration
   for (int base_slot = blockIdx.x * blockDim.x; base_slot < P.pool.n; base_slot += gridDim.x * blockDim.x) {
     const int slot = base_slot + (int)threadIdx.x;
     const bool in_range = slot < P.pool.n;
@@ -268,7 +286,7 @@ __global__ void k_unpack_tiles(long long* __restrict__ film, const uint32_t* __r
 // First surface hit -> colour = 0.5 * inter.normal + 0.5 (the interpolated, instance-transformed normal of Triangle::intersect /
 // Sphere::intersect, not the normal-mapped shading frame); miss -> the environment as at depth 0 (pt.rs:97-111); path ends.
 __global__ void __launch_bounds__(SPT_LOGIC_BLOCK) k_aov_normal(const DScene sc, const RenderParams P) {
-  if (blockIdx.x == 0 && threadIdx.x == 0) { P.ctr->it.live = 0; P.ctr->it.next_ext = 0; P.ctr->it.sq = 0; P.ctr->it.next_con = 0; P.ctr->it.n_ext = 0; P.ctr->it.drain = 0; }
+  if (blockIdx.x == 0 && threadIdx.x == 0) { P.ctr->it.live = 0; P.ctr->it.next_ext = 0; P.ctr->it.sq = 0; P.ctr->it.next_con = 0; P.ctr->it.n_ext[P.parity] = 0; P.ctr->it.drain = 0; }
   uint32_t nonfinite = 0;
   for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < P.pool.n; slot += gridDim.x * blockDim.x) {
     const uint32_t flags = P.pool.flags[slot];

@@ -420,7 +420,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   int pool_n = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(pool_cap, std::max<unsigned long long>(pool_lo, rank_samples / cap_div)); // allocated
   int pool_start = r->pool_size > 0 ? r->pool_size : (int)std::min<unsigned long long>(pool_cap, std::max<unsigned long long>(pool_lo, rank_samples / start_div)); // active at first
   pool_n = round_pool(pool_n); pool_start = std::min(pool_n, round_pool(pool_start));
-  const size_t per_slot = sizeof(PathRec) + sizeof(float4) + 3 * sizeof(float4) + sizeof(int32_t) + sizeof(uint32_t) + (SPT_NQ + 1) * sizeof(uint32_t);
+  const size_t per_slot = sizeof(PathRec) + sizeof(float4) + 3 * sizeof(float4) + sizeof(int32_t) + sizeof(uint32_t) + (SPT_NQ + 2) * sizeof(uint32_t);
   if (s->pool_n != pool_n) {
     cudaFree(s->pool_mem); s->pool_mem = nullptr; s->pool_n = 0;
     // a pool the CALLER asked for must fit; the default one shrinks (down to the 2^22 rule) if the device is short of memory
@@ -444,7 +444,8 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
     P.pool.hit_inst = (int32_t*)p; p += N * sizeof(int32_t);
     P.pool.flags = (uint32_t*)p; p += N * sizeof(uint32_t);
     P.queue = (uint32_t*)p; p += N * SPT_NQ * sizeof(uint32_t);
-    P.ext_queue = (uint32_t*)p; p += N * sizeof(uint32_t);
+    P.ext_queue[0] = (uint32_t*)p; p += N * sizeof(uint32_t);
+    P.ext_queue[1] = (uint32_t*)p; p += N * sizeof(uint32_t);
     P.pool.n = pool_start; // active slots; the arrays hold pool_n
   }
   P.ctr = s->ctr; P.film = s->film;
@@ -514,6 +515,7 @@ int render_impl(SptScene* s, const SptRenderDesc* r, float* d_mean, uint8_t* d_r
   bool con_pending = false;
   const bool aov_normal = (r->flags & SPT_RENDER_DEBUG_NORMAL) != 0;
   auto iteration = [&]() {
+    P.parity = (int)(iters & 1u); // which of the two live-slot lists this iteration writes (wavefront_types.h)
     if (aov_normal) { // pt.rs:113-118: every path ends at its first hit; no shading, no shadow rays
       spt::launch_aov_normal(ds, P, grid_gen, st);
       spt::launch_generate(ds, P, grid_gen, st);

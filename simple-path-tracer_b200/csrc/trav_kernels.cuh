@@ -23,11 +23,11 @@ SPT_D void flush_trav_counters(DevCounters* ctr, const TravCounters& tc) {
 struct ExtendSrc { // every live path of the pool: closest hit (pt.rs:49-50)
   const RenderParams& P;
   uint32_t n_rays;
-  uint32_t n_list; // 0: scan the pool slots; > 0 (draining pool): the live slots are listed in P.ext_queue[0 .. n_list)
+  uint32_t n_list; // 0: scan the pool slots; > 0 (draining pool): the live slots are listed in P.ext_queue[P.parity][0 .. n_list)
   uint32_t chunk_;
   SPT_D uint32_t chunk() const { return chunk_; }
   SPT_D uint32_t total() const { return n_list ? n_list : (uint32_t)P.pool.n; }
-  SPT_D uint32_t slot_of(uint32_t i) const { return n_list ? P.ext_queue[i] : i; }
+  SPT_D uint32_t slot_of(uint32_t i) const { return n_list ? P.ext_queue[P.parity][i] : i; }
   SPT_D void prefetch(uint32_t i) const { if (!n_list) { asm volatile(SPT_PF_INSTR ::"l"(P.pool.rec + i)); if ((i & 7u) == 0u) asm volatile("prefetch.global.L2 [%0];" ::"l"(P.pool.flags + i)); } }
   SPT_D bool load(uint32_t i, float3& o, float3& d, float& tmin, float& tmax) {
     const uint32_t s = slot_of(i);
@@ -83,7 +83,7 @@ SPT_D uint32_t spread_chunk(uint32_t n_rays, uint32_t full) {
 template <bool COUNT>
 __global__ void SPT_TRAV_BOUNDS k_extend(const DScene sc, const RenderParams P) {
   TravCounters tc = {};
-  ExtendSrc src{P, 0, P.ctr->it.drain ? P.ctr->it.n_ext : 0u, SPT_EXTEND_CHUNK};
+  ExtendSrc src{P, 0, P.ctr->it.drain ? P.ctr->it.n_ext[P.parity] : 0u, SPT_EXTEND_CHUNK};
   if (P.ctr->it.drain && src.n_list == 0u) return; // a draining pool without a live path
   if (src.n_list) src.chunk_ = spread_chunk(src.n_list, SPT_EXTEND_CHUNK);
   trace_persistent<false, COUNT>(sc, src, &P.ctr->it.next_ext, tc);

@@ -29,9 +29,12 @@ struct IterCounters { // per-iteration device counters; each is zeroed by a kern
   uint32_t live;        // live slots after generate (read by the host; zeroed by logic)
   uint32_t next_ext;    // ray-fetch cursor of extend  (zeroed by logic)
   uint32_t next_con;    // ray-fetch cursor of connect (zeroed by logic)
-  uint32_t drain;       // 1: every camera sample has been started (set by logic): generate compacts the live slots into ext_queue and extend
+  uint32_t drain;       // 1: every camera sample has been started (set by logic): generate compacts the live slots into a list and extend
                         //    fetches from that list instead of scanning a mostly empty pool
-  uint32_t n_ext;       // entries of ext_queue (producer: generate in drain mode, consumer: extend; zeroed by logic)
+  uint32_t n_ext[2];    // entries of ext_queue[parity] (producer: generate in drain mode, consumers: extend of the same iteration, logic and
+                        //    generate of the NEXT one; n_ext[parity] is zeroed by logic of its own iteration)
+  uint32_t list_valid[2]; // ext_queue[parity] lists the live slots left by that iteration (written by generate only: a kernel never reads
+                        //    the flag of its own parity, so it is stable while it runs)
 };
 struct DevCounters { // device-side totals of one render
   unsigned long long cursor;      // next camera-sample ordinal
@@ -43,7 +46,8 @@ struct RenderParams {
   PathPool pool;
   ShadowQueue sq;
   uint32_t* queue;   // SPT_NQ arrays of pool.n slot ids
-  uint32_t* ext_queue; // pool.n slot ids: the live slots of a draining pool (see IterCounters::drain)
+  uint32_t* ext_queue[2]; // pool.n slot ids each: the live slots of a draining pool (see IterCounters), one list per iteration parity
+  int32_t parity;         // iteration index & 1
   DevCounters* ctr;
   long long* film; // 3 per pixel
   const uint32_t* tiles; // owned tile ids
