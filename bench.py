@@ -79,7 +79,8 @@ def cpu_sample_size(w, h, cores):
     third of the rows on one thread (round 1 sampled 160 x 90 on 32 threads: 2 rows per band, 28 on the last) and
     measures that thread, not the machine.  At the real sizes the bands are 33 rows (last: 57) of 1080; here 4 rows each."""
     threads = 2 * cores
-    sh = min(h, 4 * threads)
+    rows = max(4, -(-32 // threads))  # 4 rows per band; more on a box with very few cores, so that the sample keeps a usable size
+    sh = min(h, rows * threads)
     sh -= sh % threads if sh >= threads else 0
     sw = max(16, int(round(sh * w / h)))
     return sw, max(1, sh), threads
