@@ -220,6 +220,29 @@ void* sim_scene_create(const SptSceneDesc* d) {
 }
 void sim_scene_destroy(void* h) { delete (spt::HostScene*)h; }
 
+// Closest hit (any = 0) or any hit (any = 1) of every ray through the compressed wide BVH, one ray at a time, in the stage order of the CUDA
+// traversal: a CPU check of the host BVH builder and of the conservative 8-bit box quantisation (tests/test_host_bvh.py compares with the oracle).
+int sim_trace(void* scene, const SptRay* rays, int64_t n, int32_t any, float* out_t, uint8_t* out_hit) {
+  const spt::HostScene& hs = *(const spt::HostScene*)scene;
+  Sim S(hs, any != 0);
+  for (int64_t i = 0; i < n; i++) {
+    Lane L;
+    out_t[i] = rays[i].t_max; out_hit[i] = 0;
+    if (hs.nodes.empty() || hs.inst.empty()) continue;
+    S.begin(L, rays[i]);
+    for (;;) {
+      bool fin = false;
+      if (S.has_node(L) && !S.has_leaf(L)) S.node(L);
+      if (S.has_leaf(L) && L.cur_inst < 0) fin = S.inst(L);
+      while (!fin && S.has_leaf(L) && L.cur_inst >= 0) fin = S.tri(L);
+      if (!fin && !S.has_node(L) && !S.has_leaf(L)) fin = S.pop(L);
+      if (fin) break;
+    }
+    out_t[i] = L.tmax; out_hit[i] = L.hit ? 1 : 0;
+  }
+  return 0;
+}
+
 int sim_run(void* scene, const SptRay* rays, int64_t n, const SimCfg* cfg, SimOut* out) {
   const spt::HostScene& hs = *(const spt::HostScene*)scene;
   Sim S(hs, cfg->any != 0);

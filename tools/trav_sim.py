@@ -37,6 +37,7 @@ def build():
     L.sim_scene_create.argtypes = [C.c_void_p]
     L.sim_scene_destroy.argtypes = [C.c_void_p]
     L.sim_run.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(Cfg), C.POINTER(Out)]
+    L.sim_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]
     return L
 
 
